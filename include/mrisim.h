@@ -1,0 +1,218 @@
+/*
+ * mrisim.h -- C ABI of the B200-native walker/T2-signal path.
+ *
+ * The reference (RabinKarp/MRI_Nanoparticle_Simulation) has no FFI of its own; its only
+ * seam is C++: `void simulateWaters(std::string)` (src/cuda_sim.h:74), which consumes the
+ * accessors of SimulationBox (src/SimulationBox.cpp:536-594) and compile-time knobs from
+ * src/parameters.h.  This header is that seam restated as plain C: every entry point below
+ * names the reference interface it replaces.  No C++/torch types cross the boundary; all
+ * arrays are caller-owned and copied by the callee unless stated otherwise.
+ *
+ * Return convention: 0 = ok, non-zero = error (text via mrisim_last_error()).  The
+ * reference aborts through HANDLE_ERROR on the one CUDA call it checks
+ * (src/cuda_sim.cu:407) and ignores every other status; here every call is checked.
+ *
+ * There is NO CPU fallback behind any device entry point: without a CUDA device (or with
+ * a failing kernel) they return an error.
+ */
+#ifndef MRISIM_H
+#define MRISIM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRISIM_VERSION 100  /* 0.1.0 */
+
+/* -------------------------------------------------------------------------------------
+ * Parameters: run-time mirror of `struct ParameterStruct` (src/parameters.h:25-126) plus
+ * the three file-scope constants of src/cuda_sim.cu:44-45 (pInt, pfreq).  Field names are
+ * the reference's.  Derived fields (t, tcp, pfreq, in_stdev, out_stdev) are filled by
+ * mrisim_params_derive() with the reference's own expressions.
+ * ----------------------------------------------------------------------------------- */
+enum { MRISIM_KICK_NONE = 0, MRISIM_KICK_RANDOM = 1, MRISIM_KICK_CONSTANT = 2 };
+
+typedef struct mrisim_params {
+    double  g;                  /* parameters.h:27  gyromagnetic ratio                  */
+    double  scale;              /* :30  explicit-field radius in units of cell_r        */
+    double  border;             /* :33  periodic-image cutoff (um)                      */
+    int32_t num_threads;        /* :36  host threads for the octree build               */
+    int32_t sprintSteps;        /* :42  steps per sprint (signal flush / all-reduce)    */
+    int32_t num_water;          /* :46                                                  */
+    int32_t num_cells;          /* :49                                                  */
+    double  cell_r;             /* :50                                                  */
+    double  mmoment;            /* :52                                                  */
+    int32_t kick_mode;          /* :55-56  RANDOM_KICK / CONSTANT_KICK                  */
+    int32_t avoid_intracellular_throw; /* :77  #define AVOID_INTRACELLULAR_THROW        */
+    double  phase_stdev;        /* :61                                                  */
+    double  phase_k;            /* :59 / :62                                            */
+    double  bound;              /* :66                                                  */
+    double  water_start_bound;  /* :71                                                  */
+    int32_t hashDim;            /* :80                                                  */
+    int32_t maxNeighbors;       /* :81                                                  */
+    double  D_cell;             /* :84                                                  */
+    double  D_extra;            /* :85                                                  */
+    double  P_expr;             /* :86                                                  */
+    double  tau;                /* :88                                                  */
+    int32_t totaltime;          /* :91                                                  */
+    int32_t t;                  /* :93  (int)(totaltime/tau)                            */
+    double  taucp;              /* :94                                                  */
+    int32_t tcp;                /* :95  (int)(taucp/tau)                                */
+    int32_t pfreq;              /* cuda_sim.cu:44-45  (int)(1e-3/tau)                   */
+    double  reflectIO;          /* :100,116                                             */
+    double  reflectOI;          /* :101,117                                             */
+    double  in_stdev;           /* :104,120  sqrt(pi*D_cell*tau)                        */
+    double  out_stdev;          /* :105,121  sqrt(pi*D_extra*tau)                       */
+} mrisim_params;
+
+/* shipped src/parameters.h values (num_water 4032, sprintSteps 20000, 270 cells, ...) */
+void mrisim_params_default(mrisim_params* p);
+/* recompute t, tcp, pfreq, in_stdev, out_stdev from the primaries (parameters.h:93,95,120-121) */
+void mrisim_params_derive(mrisim_params* p);
+/* the commented low-permeability formulas of parameters.h:116-117 (BASELINE config 3) */
+void mrisim_params_low_permeability(mrisim_params* p);
+
+/* -------------------------------------------------------------------------------------
+ * POD records.  Layout-compatible with the reference structs so that
+ * SimulationBox::getWaters()/getMNPs()/getCells() pointers can be handed over directly.
+ * ----------------------------------------------------------------------------------- */
+typedef struct mrisim_water {   /* water_info, src/rand_walk.h:25-53 (40 bytes)          */
+    double  x, y, z;
+    double  phase;
+    uint8_t in_cell;            /* bool */
+    uint8_t _pad[3];
+    int32_t nearest;
+} mrisim_water;
+
+typedef struct mrisim_mnp {     /* MNP_info, src/rand_walk.h:58-69 (40 bytes)            */
+    double x, y, z, r, M;
+} mrisim_mnp;
+
+typedef struct mrisim_node {    /* oct_node, src/octree.h:28-33, resident vector flattened */
+    uint64_t mc;                /* Morton code; bit 63 = leaf; bit 3*depth = depth marker */
+    uint32_t child[8];          /* internal: offset RELATIVE to this node (octree.cpp:320);
+                                   leaf: IEEE-754 bits of the 8 float B samples           */
+    uint32_t res_start;         /* first resident in the residents array                 */
+    uint32_t n_res;             /* resident count (0 for internal nodes)                 */
+} mrisim_node;
+
+/* per-walker RNG state of the walker stream contract (see mrisim_math.h) */
+typedef struct mrisim_rng_state {
+    uint64_t s0, s1;            /* xoroshiro128+ state (src/xorshift.h:129-141)          */
+    double   spare;             /* second Box-Muller normal, consumed at odd steps       */
+} mrisim_rng_state;
+
+/* -------------------------------------------------------------------------------------
+ * Host scene: replaces `BacteriaBox simBox(&gen); simBox.populateSimulation();`
+ * (src/cuda_sim.cu:920-921 -> SimulationBox.cpp:77-97, BacteriaBox.cpp:49-121,
+ * octree.cpp:388-450).  host_seed replaces `time(NULL) + rd()` (cuda_sim.cu:911-912).
+ * n_threads <= 0 means "all hardware threads"; the result does not depend on it.
+ * ----------------------------------------------------------------------------------- */
+typedef struct mrisim_scene mrisim_scene;
+
+int  mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads,
+                        mrisim_scene** out);
+int  mrisim_scene_load(const char* path, mrisim_scene** out);     /* MRISCN01 file */
+int  mrisim_scene_save(const mrisim_scene* s, const char* path);
+void mrisim_scene_free(mrisim_scene* s);
+const char* mrisim_scene_last_error(void);
+
+/* accessors -- SimulationBox::getCells/getMNPs/getMNPCount/getLookupTable/getWaters/
+ * getOctree (SimulationBox.cpp:536-594).  Pointers stay valid until mrisim_scene_free. */
+const double*       mrisim_scene_cells(const mrisim_scene* s, int32_t* num_cells);          /* Triple[num_cells] */
+const mrisim_mnp*   mrisim_scene_mnps(const mrisim_scene* s, int32_t* num_mnps);
+const int32_t*      mrisim_scene_lookup(const mrisim_scene* s, int32_t* hashDim, int32_t* maxNeighbors); /* rows contiguous, -1 padded */
+const mrisim_water* mrisim_scene_waters(const mrisim_scene* s, int32_t* num_water);         /* Morton-sorted */
+int  mrisim_scene_octree(const mrisim_scene* s, int32_t* min_depth, int32_t* max_depth,
+                         const uint32_t** subtree_sizes, int32_t* n_subtrees,
+                         const mrisim_node** nodes, uint64_t* n_nodes,
+                         const mrisim_mnp** residents, uint64_t* n_res);
+/* replace the waters of a scene: re-throws `num_water` waters continuing the scene's host
+ * RNG stream is NOT what this does -- it throws from a fresh XORShift(seed) so that
+ * benchmark-size walker sets (1M..16M) can be generated per rank without rebuilding the
+ * octree.  BacteriaBox::init_waters + SimulationBox::sortWaters semantics otherwise. */
+int  mrisim_scene_rethrow_waters(mrisim_scene* s, const mrisim_params* p, int64_t num_water,
+                                 uint64_t seed, int sort_by_morton);
+
+/* -------------------------------------------------------------------------------------
+ * Device context: replaces the body of simulateWaters() between populateSimulation() and
+ * `fout <<` (src/cuda_sim.cu:923-1024).
+ * ----------------------------------------------------------------------------------- */
+typedef struct mrisim_ctx mrisim_ctx;
+
+/* field-evaluation arithmetic of the resident-dipole sum (cuda_sim.cu:107-114) */
+enum {
+    MRISIM_FIELD_EXACT = 0,     /* IEEE sqrt + divide, unfused: bit-identical to the oracle  */
+    MRISIM_FIELD_FAST  = 1      /* rsqrt/FMA form: same positions/indices, phase within 1e-12 */
+};
+
+/* initGPUParams (cuda_sim.cu:406-408) + `Handler handle(0)` (:916). */
+int  mrisim_create(const mrisim_params* p, int device, mrisim_ctx** out);
+void mrisim_destroy(mrisim_ctx* ctx);                 /* finalizeGPU (cuda_sim.cu:430-433) */
+const char* mrisim_last_error(const mrisim_ctx* ctx); /* ctx may be NULL: last create error */
+int  mrisim_set_field_mode(mrisim_ctx* ctx, int mode);
+
+/* `p_array<Triple> dev_lattice(p.num_cells, simBox.getCells(), d.lattice)` (cuda_sim.cu:935,960) */
+int  mrisim_set_cells(mrisim_ctx* ctx, const double* xyz, int32_t num_cells);
+/* cpyLookupDevice (cuda_sim.cu:849-861): rows[hashDim^3][maxNeighbors], -1 terminated   */
+int  mrisim_set_lookup(mrisim_ctx* ctx, const int32_t* rows, int32_t hashDim, int32_t maxNeighbors);
+/* initOctree (cuda_sim.cu:296-369): forest of 8^min_depth DFS node vectors              */
+int  mrisim_set_octree(mrisim_ctx* ctx, int32_t min_depth, int32_t max_depth,
+                       const uint32_t* subtree_sizes, int32_t n_subtrees,
+                       const mrisim_node* nodes, uint64_t n_nodes,
+                       const mrisim_mnp* residents, uint64_t n_res);
+/* the three calls above from one mrisim_scene */
+int  mrisim_set_scene(mrisim_ctx* ctx, const mrisim_scene* s);
+
+/* `p_array<water_info> dev_waters(p.num_water, simBox.getWaters(), d.waters)` (cuda_sim.cu:934,961).
+ * Walker i of this call is GLOBAL walker first_walker_id + i; its random stream is
+ * XORShift(walker_seed + global id) (contract in mrisim_math.h), so a run sharded over
+ * several contexts/GPUs draws exactly the numbers of the unsharded run.  Resets time to 0. */
+int  mrisim_set_waters(mrisim_ctx* ctx, const mrisim_water* waters, uint64_t n,
+                       uint64_t walker_seed, uint64_t first_walker_id);
+/* d.waters read-back (cuda_sim.cu:744) */
+int  mrisim_get_waters(mrisim_ctx* ctx, mrisim_water* out, uint64_t n);
+/* checkpoint/resume of the walker streams and the step counter (no reference analogue) */
+int  mrisim_get_rng(mrisim_ctx* ctx, mrisim_rng_state* out, uint64_t n);
+int  mrisim_set_rng(mrisim_ctx* ctx, const mrisim_rng_state* in, uint64_t n);
+int64_t mrisim_get_time(const mrisim_ctx* ctx);       /* steps simulated so far (`time`, cuda_sim.cu:973,1015) */
+int  mrisim_set_time(mrisim_ctx* ctx, int64_t time_steps);
+
+/* One iteration of the sprint loop (cuda_sim.cu:974-1024) minus the CSV line: `steps`
+ * timesteps (a multiple of pfreq), writing steps/pfreq signal samples
+ * S_k = sum_w cos(phase_w) to signal_out (HOST memory), CPMG flips applied after sampling
+ * whenever time % tcp == 0.  Synchronous. */
+int  mrisim_run_sprint(mrisim_ctx* ctx, int32_t steps, double* signal_out);
+/* Same, asynchronous on `cuda_stream` (a cudaStream_t; NULL = the context's own stream),
+ * samples written to DEVICE memory signal_out_dev (steps/pfreq doubles, e.g. a buffer a
+ * collective library will all-reduce).  The caller synchronises. */
+int  mrisim_run_sprint_async(mrisim_ctx* ctx, int32_t steps, double* signal_out_dev, void* cuda_stream);
+
+/* Test hook: a sprint that also records, for every (step, walker), position, in_cell and
+ * the flat octree leaf index (= subtree_prefix[i] + j of the reference's (i, j)).  Arrays
+ * are HOST memory, step-major [steps][n]; any pointer may be NULL. */
+int  mrisim_trace_sprint(mrisim_ctx* ctx, int32_t steps, double* signal_out,
+                         double* x, double* y, double* z, uint8_t* in_cell, uint32_t* leaf);
+
+/* kernels launched by this context so far (bench.py's gpu_launches claim) */
+uint64_t mrisim_kernel_launches(const mrisim_ctx* ctx);
+/* device-timed duration (ms, CUDA events on the launch stream) of the last sprint's walker kernel */
+float mrisim_last_sprint_kernel_ms(mrisim_ctx* ctx);
+
+/* CSV row exactly as `fout << ((double) time * p.tau) << delim << target << endl`
+ * (cuda_sim.cu:1022, parameters.h:129).  Returns the number of bytes written (incl. '\n'). */
+int  mrisim_csv_row(int64_t time_steps, double tau, double target, char* buf, size_t buflen);
+
+/* FP64 pipe micro-benchmark used as the roofline denominator: dependent-free DFMA chains
+ * on every SM; returns achieved FP64 FMA TFLOP/s (2 flop per FMA) or <0 on error. */
+double mrisim_measure_fp64_tflops(int device, int iters);
+
+int mrisim_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRISIM_H */
