@@ -206,6 +206,15 @@ float mrisim_last_sprint_kernel_ms(mrisim_ctx* ctx);
  * (cuda_sim.cu:1022, parameters.h:129).  Returns the number of bytes written (incl. '\n'). */
 int  mrisim_csv_row(int64_t time_steps, double tau, double target, char* buf, size_t buflen);
 
+/* The whole of simulateWaters(fName) (cuda_sim.cu:902-1034) as one call: build the scene
+ * from host_seed, upload, run max_sprints sprints (<0: all t/sprintSteps of them) on
+ * `device`, write the CSV to `filename`, print the reference's banners and the elapsed
+ * time of the sprint loop.  host_seed / walker_seed replace time(NULL)+rd() (:911-912) and
+ * the cuRAND seed time(NULL) (gpu_random.cu:22).  The C++ drop-in
+ * `void simulateWaters(std::string)` (csrc/simulate_waters.cpp) forwards here. */
+int  mrisim_simulate_waters(const char* filename, const mrisim_params* p, uint64_t host_seed,
+                            uint64_t walker_seed, int device, int64_t max_sprints);
+
 /* FP64 pipe micro-benchmark used as the roofline denominator: dependent-free DFMA chains
  * on every SM; returns achieved FP64 FMA TFLOP/s (2 flop per FMA) or <0 on error. */
 double mrisim_measure_fp64_tflops(int device, int iters);

@@ -123,3 +123,23 @@ class Oracle:
         ic = C.c_int()
         n = lib().oracle_probe_nearest(C.byref(self.params), C.byref(self.sc), x, y, z, C.byref(ic))
         return n, ic.value
+
+
+class _SceneView:
+    """Adapter: the arrays of a product BacteriaBox in the attribute layout Oracle expects."""
+
+    def __init__(self, box):
+        oct_ = box.getOctree()
+        self.cells = box.getCells()
+        self.lookup = box.getLookupTable()
+        self.subtree_sizes = oct_.subtree_sizes
+        self.nodes = oct_.nodes
+        self.residents = oct_.residents
+        self.num_cells = len(self.cells)
+        self.min_depth, self.max_depth = oct_.min_depth, oct_.max_depth
+        self.n_subtrees = len(oct_.subtree_sizes)
+        self.n_nodes = len(oct_.nodes)
+
+
+def oracle_for_box(box, params) -> Oracle:
+    return Oracle(_SceneView(box), params)
