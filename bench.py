@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py -- walker-steps/s of the sprint hot path on N B200s (one process per GPU).
+
+    python bench.py --gpus 1 --steps K --warmup W
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...        (CPU arm: the oracle port on all host cores)
+
+A "step" is ONE SPRINT: `sprintSteps` (20 000) timesteps of every walker on this rank --
+Gaussian step, membrane test, octree field lookup, phase kick, 20 signal samples -- plus,
+for N > 1, the one all-reduce of the 20 signal partials (NCCL).  Workload (config.workload):
+BASELINE.json configs[3], the configuration the 1/2/4/8-GPU metric is quoted on: 1 Mi waters
+per GPU in the dense 2000-cell box (SURVEY.md 8d "4a": hashDim 40, maxNeighbors 16, 89 448
+octree nodes).  Walkers are independent, so ranks own disjoint walker ranges of one global
+index space (weak scaling: 1 Mi walkers per GPU), the scene is replicated.
+
+Timing: W untimed warm-up sprints, then K sprints, each bracketed by CUDA events on the
+stream the kernels are launched on (torch's current stream, handed to the C ABI), with an
+L2 flush (256 MiB write) between sprints outside the event pairs; barrier +
+torch.cuda.synchronize() on both sides of the timed region; max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (knob overrides, scene seed, walkers per GPU)
+    "cfg4a_dense2000cells_1Mi_waters_per_gpu": (dict(num_cells=2000, hashDim=40, maxNeighbors=16), 11, 1 << 20),
+    "cfg1_default_4032_waters": (dict(), 12345, 4032),
+    "cfg2_8000_waters_intracellular_kick": (dict(num_water=8000, avoid_intracellular_throw=0), 21, 8000),
+    "cfg3_lowperm_100k_waters": (dict(), 12345, 100000),
+    "default_scene_1Mi_waters_per_gpu": (dict(), 12345, 1 << 20),
+}
+DEFAULT_WORKLOAD = "cfg4a_dense2000cells_1Mi_waters_per_gpu"
+WALKER_SEED = 0xC0FFEE
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ----------------------------------------------------------------------------------------
+def make_params(api, name):
+    over, seed, n = WORKLOADS[name]
+    p = api.ParameterStruct(**over)
+    if name.startswith("cfg3"):
+        api.low_permeability(p)
+    return p, seed, n
+
+
+def get_scene(api, name, rank, world, barrier):
+    """Rank 0 builds the scene once (host octree build: ~15 s for 2000 cells on 8 cores) and
+    saves it; the other ranks load the file."""
+    p, seed, n = make_params(api, name)
+    path = f"/tmp/mrisim_bench_{name}_seed{seed}.scn"
+    if rank == 0 and not os.path.exists(path):
+        t = time.time()
+        q = p.copy(); q.num_water = 64
+        box = api.BacteriaBox(q, seed).populateSimulation()
+        box.save(path + ".tmp"); os.replace(path + ".tmp", path)
+        log(f"[bench] scene {name} built in {time.time() - t:.1f} s -> {path}")
+    barrier()
+    box = api.BacteriaBox.load(path, p)
+    return box, p, n
+
+
+def throw_waters(box, p, n, rank):
+    """This rank's walkers: BacteriaBox::init_waters + sortWaters from XORShift(7000 + rank)."""
+    box.rethrow_waters(n, 7000 + rank, True, p)
+    return box.getWaters().copy()
+
+
+def workload_stats(box, p, waters, sample=4000):
+    """C (lookup candidates), L (levels below min_depth), R (leaf residents) at the walkers'
+    current positions -- the variables of the algorithmic op count F = 73 + 9C + 9L + 24R
+    (SURVEY.md 8d).  Pure numpy/python on the product scene arrays."""
+    oct_ = box.getOctree()
+    nodes, prefix = oct_.nodes, oct_.subtree_prefix
+    lut = box.getLookupTable()
+    rng = np.random.default_rng(0)
+    idx = rng.choice(len(waters), size=min(sample, len(waters)), replace=False)
+    Cs, Ls, Rs = [], [], []
+    h, cube = p.hashDim, p.bound / p.hashDim
+    md = oct_.min_depth
+    for i in idx:
+        x, y, z = float(waters["x"][i]), float(waters["y"][i]), float(waters["z"][i])
+        row = (int(z / cube) * h + int(y / cube)) * h + int(x / cube)
+        Cs.append(int((lut[row] != -1).sum()))
+        m = [int(np.floor(v / p.bound * (1 << 21))) for v in (x, y, z)]
+        code = 0
+        for b in range(md):
+            sh = 20 - b
+            code = (code << 3) | (((m[0] >> sh) & 1) << 2) | (((m[1] >> sh) & 1) << 1) | ((m[2] >> sh) & 1)
+        n, d = int(prefix[code]), md
+        while not (int(nodes["mc"][n]) >> 63):
+            sh = 20 - d
+            c = (((m[0] >> sh) & 1) << 2) | (((m[1] >> sh) & 1) << 1) | ((m[2] >> sh) & 1)
+            n += int(nodes["child"][n][c]); d += 1
+        Ls.append(d - md); Rs.append(int(nodes["n_res"][n]))
+    return float(np.mean(Cs)), float(np.mean(Ls)), float(np.mean(Rs))
+
+
+#: FP64 operations of the contract's Gaussian transform per walker-step (half a Box-Muller
+#: pair: ln 27, sqrt 1, sincos 33, glue 5 -> 66 per pair) + 7 uniform conversions (1 sub each
+#: incl. the 1-u1) -- counted from include/mrisim_math.h, one op per + - * / sqrt fma.
+RNG_FP64_OPS_PER_STEP = 66 / 2 + 6
+
+
+def algorithmic_ops(Cbar, Lbar, Rbar):
+    return 73 + 9 * Cbar + 9 * Lbar + 24 * Rbar + RNG_FP64_OPS_PER_STEP
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+def cpu_arm(api, ol, box, p, waters, budget_s, n_threads, steps):
+    """Time the oracle port (CPU restatement of the reference's device functions; the
+    reference has no CPU walk of its own) on a bounded walker sample."""
+    orc = ol.oracle_for_box(box, p)
+    calib_n = min(len(waters), 64 * n_threads)
+    w = waters[:calib_n].copy(); rng = orc.seed(calib_n, WALKER_SEED)
+    t = time.perf_counter(); orc.run_sprint(w, rng, 0, p.pfreq, n_threads=n_threads); dt = time.perf_counter() - t
+    rate = calib_n * p.pfreq / max(dt, 1e-9)
+    n = int(min(len(waters), max(n_threads, rate * budget_s / steps)))
+    n -= n % n_threads or 0
+    n = max(n, n_threads)
+    return orc, n, rate
+
+
+def run_reference_arm(args, api, ol):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n_threads = os.cpu_count() or 1
+    box, p, n_per_gpu = get_scene(api, args.workload, 0, 1, lambda: None)
+    waters = throw_waters(box, p, min(n_per_gpu, 1 << 18), 0)
+    steps = p.sprintSteps
+    per_step_budget = max(2.0, min(20.0, 150.0 / max(args.steps + args.warmup, 1)))
+    orc, n, _ = cpu_arm(api, ol, box, p, waters, per_step_budget, n_threads, steps)
+    w = waters[:n].copy(); rng = orc.seed(n, WALKER_SEED)
+    time0 = 0
+    for _ in range(args.warmup):
+        orc.run_sprint(w, rng, time0, steps, n_threads=n_threads); time0 += steps
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        orc.run_sprint(w, rng, time0, steps, n_threads=n_threads); time0 += steps
+    dt = time.perf_counter() - t
+    value = n * steps * args.steps / dt
+    sample = f"{n} of the workload's walkers x {steps} timesteps per step (one full sprint), {n_threads} pthreads over walkers"
+    line = {
+        "impl": "reference", "metric": "walker-steps/sec", "value": value, "unit": "walker-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "sprintSteps": steps, "walkers_in_sample": n,
+                   "note": "reference has no CPU walk (SURVEY.md D1): CPU restatement of its device functions (oracle port) "
+                           "over scene arrays from the reference-identical host builder"},
+        "cpu_baseline": {"value": value, "unit": "walker-steps/s", "cores": n_threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "walker-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--walkers-per-gpu", type=int, default=0, help="override the workload's walker count")
+    ap.add_argument("--field-mode", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        log("[bench] note: W < 3 warm-up steps does not meet the timing rules")
+
+    from mri_nanoparticle_simulation_b200 import api
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    if args.impl == "reference":
+        import oracle_lib as ol          # the one other place bench.py may execute oracle/
+        return run_reference_arm(args, api, ol)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+
+    box, p, n_per_gpu = get_scene(api, args.workload, rank, world, barrier)
+    if args.walkers_per_gpu:
+        n_per_gpu = args.walkers_per_gpu
+    waters = throw_waters(box, p, n_per_gpu, rank)
+    steps = p.sprintSteps
+    n_int = steps // p.pfreq
+    ctx = api.WalkerContext(p, local)
+    ctx.set_field_mode(api.FIELD_FAST if args.field_mode == "fast" else api.FIELD_EXACT)
+    ctx.set_scene(box)
+    ctx.set_waters(waters, WALKER_SEED, rank * n_per_gpu)
+
+    stream = torch.cuda.current_stream()
+    sig = torch.zeros(n_int, dtype=torch.float64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def one_step():
+        ctx.run_sprint_async(steps, sig.data_ptr(), stream.cuda_stream)
+        if world > 1:
+            dist.all_reduce(sig)            # the path's only exchange: 20 doubles per sprint
+
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize(); barrier()
+
+    fp64_peak = api.measure_fp64_tflops(local)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    launches0 = ctx.kernel_launches
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kernel_ms = []
+    torch.cuda.synchronize(); barrier()
+    wall0 = time.perf_counter()
+    for a, b in ev:
+        flush.fill_(1)                       # L2 flush between timed iterations (not inside an event pair)
+        a.record(stream)
+        one_step()
+        b.record(stream)
+        b.synchronize()
+        kernel_ms.append(ctx.last_sprint_kernel_ms())
+    torch.cuda.synchronize(); barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if sampler else None
+    launches = ctx.kernel_launches - launches0
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_s = float(total_ms.item()) * 1e-3
+    n_total = n_per_gpu * world
+    value = n_total * steps * args.steps / total_s
+    signal_last = sig.cpu().numpy().copy()
+
+    # ---- e2e: the same sprint through the host-buffer C-ABI calls a user makes ----------
+    host_w = ctx.get_waters()
+    h2d = host_w.nbytes; d2h = host_w.nbytes + n_int * 8
+    e2e_steps = max(1, min(args.steps, 3))
+    torch.cuda.synchronize(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.set_waters(host_w, WALKER_SEED, rank * n_per_gpu)       # H2D of the walker records (pinned staging)
+        part = ctx.run_sprint(steps)                                 # D2H of the 20 samples
+        if world > 1:
+            t = torch.from_numpy(part).to(dev); dist.all_reduce(t); part = t.cpu().numpy()
+        host_w = ctx.get_waters()                                    # D2H of the walker records
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = n_total * steps * e2e_steps / float(e2e_s.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    Cbar, Lbar, Rbar = workload_stats(box, p, host_w)
+    F = algorithmic_ops(Cbar, Lbar, Rbar)
+    k_ms = float(np.mean(kernel_ms))
+    achieved = n_per_gpu * steps * F / (k_ms * 1e-3) / 1e12
+    traffic = None
+    prof = os.path.join(ROOT, "profiles", "traffic_r01.json")
+    if os.path.exists(prof):
+        try:
+            traffic = json.load(open(prof)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    line = {
+        "metric": "walker-steps/sec", "value": value, "unit": "walker-steps/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "walkers_per_gpu": n_per_gpu, "walkers_total": n_total,
+                   "sprintSteps": steps, "signal_samples_per_step": n_int, "num_cells": p.num_cells,
+                   "octree_nodes": int(len(box.getOctree().nodes)), "field_mode": args.field_mode,
+                   "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
+                   "parallelism": f"walker-sharded x{world}, scene replicated, 1 all-reduce of {n_int} f64 per step"},
+        "e2e": {"value": e2e_value, "unit": "walker-steps/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "steps": e2e_steps, "call": "mrisim_set_waters + mrisim_run_sprint + mrisim_get_waters (host buffers)"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
+                     "traffic": traffic, "kernel": "walker_sprint_kernel", "kernel_ms": k_ms,
+                     "algorithmic_fp64_ops_per_walker_step": F, "C_L_R": [Cbar, Lbar, Rbar],
+                     "peak_source": "measured live: mrisim_measure_fp64_tflops (8 independent DFMA chains/thread, all SMs); "
+                                    "MEASURED_PEAKS.json has no FP64 entry",
+                     "note": "path is FP64-pipe bound, not HBM/tensor (SURVEY.md 8d): per-step HBM traffic is ~0"},
+        "signal_last_step": [float(v) for v in signal_last[:3]],
+        "wall_s_timed_region": wall,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        import oracle_lib as ol          # cpu_baseline leg: the oracle as the thing timed on the host cores
+        n_threads = os.cpu_count() or 1
+        orc, n, _ = cpu_arm(api, ol, box, p, waters, args.cpu_budget_s, n_threads, steps)
+        w = waters[:n].copy(); rng = orc.seed(n, WALKER_SEED)
+        t = time.perf_counter(); orc.run_sprint(w, rng, 0, steps, n_threads=n_threads); dt = time.perf_counter() - t
+        line["cpu_baseline"] = {"value": n * steps / dt, "unit": "walker-steps/s", "cores": n_threads, "kind": "port",
+                                "sample": f"first {n} walkers of rank 0 x {steps} timesteps (one sprint), {dt:.1f} s, "
+                                          f"{n_threads} pthreads over walkers"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

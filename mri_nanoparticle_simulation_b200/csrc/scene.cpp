@@ -25,6 +25,9 @@
 #include "mrisim.h"
 #include "mrisim_math.h"
 
+static_assert(sizeof(mrisim_params) == 192 && sizeof(mrisim_water) == 40 && sizeof(mrisim_mnp) == 40 &&
+              sizeof(mrisim_node) == 48 && sizeof(mrisim_rng_state) == 24, "C ABI layouts (mirrored in _cabi.py)");
+
 namespace {
 
 thread_local std::string g_scene_error;

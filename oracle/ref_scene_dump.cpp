@@ -86,8 +86,22 @@ int main(int argc, char** argv) {
     for (int i = 0; i < p.num_water; i++) { put(f, w[i].x); put(f, w[i].y); put(f, w[i].z); put(f, w[i].phase); }
     fclose(f);
 
-    // A.6-style probe: leaf holding (15,15,15) and the reference host field there.
-    if (argc > 3) {
+    // Probes of the reference's own host traversal: argv[3] = file of (x,y,z) double
+    // triples, argv[4] = output of (uint64 leaf mc, double Octree::get_field) pairs.
+    if (argc > 4) {
+        FILE* in = fopen(argv[3], "rb");
+        FILE* out = fopen(argv[4], "wb");
+        if (!in || !out) { perror("probe files"); return 1; }
+        double q3[3];
+        while (fread(q3, sizeof(double), 3, in) == 3) {
+            water_info q; q.x = q3[0]; q.y = q3[1]; q.z = q3[2];
+            oct_node* leaf = oct->get_voxel(&q);
+            put<uint64_t>(out, leaf->mc);
+            put<double>(out, oct->get_field(&q, leaf));
+        }
+        fclose(in); fclose(out);
+    } else if (argc > 3) {
+        // A.6-style probe: leaf holding (15,15,15) and the reference host field there.
         water_info q; q.x = q.y = q.z = 15.0;
         oct_node* leaf = oct->get_voxel(&q);
         printf("PROBE mc=%016llx field=%.17g\n", (unsigned long long)leaf->mc, oct->get_field(&q, leaf));
