@@ -257,7 +257,8 @@ def main():
     ctx.set_scene(box)
     ctx.set_waters(waters, WALKER_SEED, rank * n_per_gpu)
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)       # everything timed runs on this one stream
+    torch.cuda.set_stream(stream)
     sig = torch.zeros(n_int, dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 

@@ -186,10 +186,12 @@ int  mrisim_set_time(mrisim_ctx* ctx, int64_t time_steps);
  * S_k = sum_w cos(phase_w) to signal_out (HOST memory), CPMG flips applied after sampling
  * whenever time % tcp == 0.  Synchronous. */
 int  mrisim_run_sprint(mrisim_ctx* ctx, int32_t steps, double* signal_out);
-/* Same, asynchronous on `cuda_stream` (a cudaStream_t; NULL = the context's own stream),
- * samples written to DEVICE memory signal_out_dev (steps/pfreq doubles, e.g. a buffer a
- * collective library will all-reduce).  The caller synchronises. */
+/* Same, asynchronous on `cuda_stream` (a cudaStream_t; NULL is CUDA's legacy default stream,
+ * as everywhere in CUDA; mrisim_ctx_stream() returns the context's own), samples written to
+ * DEVICE memory signal_out_dev (steps/pfreq doubles, e.g. a buffer a collective library will
+ * all-reduce).  The caller synchronises that stream before touching walker state. */
 int  mrisim_run_sprint_async(mrisim_ctx* ctx, int32_t steps, double* signal_out_dev, void* cuda_stream);
+void* mrisim_ctx_stream(mrisim_ctx* ctx);     /* the cudaStream_t the synchronous calls use */
 
 /* Test hook: a sprint that also records, for every (step, walker), position, in_cell and
  * the flat octree leaf index (= subtree_prefix[i] + j of the reference's (i, j)).  Arrays

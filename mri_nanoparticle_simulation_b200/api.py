@@ -72,6 +72,7 @@ def lib():
         "mrisim_set_time": (C.c_int, [vp, i64]),
         "mrisim_run_sprint": (C.c_int, [vp, i32, vp]),
         "mrisim_run_sprint_async": (C.c_int, [vp, i32, vp, vp]),
+        "mrisim_ctx_stream": (vp, [vp]),
         "mrisim_trace_sprint": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp]),
         "mrisim_kernel_launches": (u64, [vp]),
         "mrisim_last_sprint_kernel_ms": (C.c_float, [vp]),
@@ -95,7 +96,7 @@ ABI_SYMBOLS = [
     "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
-    "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async",
+    "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
     "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops",
 ]
@@ -300,7 +301,8 @@ class WalkerContext:
 
     def run_sprint_async(self, steps: int, signal_dev_ptr: int, stream: int = 0):
         """signal_dev_ptr: device pointer to steps/pfreq doubles (e.g. tensor.data_ptr());
-        stream: a cudaStream_t handle (e.g. torch.cuda.current_stream().cuda_stream)."""
+        stream: a cudaStream_t handle (e.g. torch.cuda.current_stream().cuda_stream; 0 is
+        CUDA's legacy default stream)."""
         self._ck(lib().mrisim_run_sprint_async(self._h, steps, signal_dev_ptr, stream))
 
     def trace_sprint(self, steps: int):
