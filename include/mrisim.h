@@ -221,6 +221,14 @@ int  mrisim_simulate_waters(const char* filename, const mrisim_params* p, uint64
  * on every SM; returns achieved FP64 FMA TFLOP/s (2 flop per FMA) or <0 on error. */
 double mrisim_measure_fp64_tflops(int device, int iters);
 
+/* Device self-test of the constant-divisor division used for x/bound and x/cubeLength:
+ * compares it with the IEEE divide for 3n numerators in [0, 3b); returns the number of
+ * mismatches (0 expected), <0 on error. */
+int64_t mrisim_selftest_div(int device, double b, uint64_t n);
+/* Same for the branch-free correctly rounded sqrt / divide of the resident loop: n random x in
+ * [lo, hi] (sqrt(x), t/(x*x*sqrt(x)), t/x against the compiler's IEEE sqrt and divide). */
+int64_t mrisim_selftest_sqrt_div(int device, double lo, double hi, uint64_t n);
+
 int mrisim_version(void);
 
 #ifdef __cplusplus

@@ -19,7 +19,7 @@ from . import _cabi as cabi
 from ._cabi import FIELD_EXACT, FIELD_FAST, KICK_CONSTANT, KICK_NONE, KICK_RANDOM, Params  # noqa: F401
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libmrisim.so")
+LIB_PATH = os.environ.get("MRISIM_LIB") or os.path.join(PKG, "libmrisim.so")   # MRISIM_LIB: tuning builds only
 
 _lib = None
 
@@ -78,6 +78,8 @@ def lib():
         "mrisim_last_sprint_kernel_ms": (C.c_float, [vp]),
         "mrisim_csv_row": (C.c_int, [i64, dbl, dbl, C.c_char_p, C.c_size_t]),
         "mrisim_measure_fp64_tflops": (dbl, [C.c_int, C.c_int]),
+        "mrisim_selftest_div": (i64, [C.c_int, dbl, u64]),
+        "mrisim_selftest_sqrt_div": (i64, [C.c_int, dbl, dbl, u64]),
         "mrisim_simulate_waters": (C.c_int, [C.c_char_p, PP, u64, u64, C.c_int, i64]),
     }
     for name, (res, args) in sig.items():
@@ -98,7 +100,7 @@ ABI_SYMBOLS = [
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
-    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops",
+    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div",
 ]
 
 

@@ -16,14 +16,17 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 INC = os.path.join(ROOT, "include")
-OBJ = os.path.join(PKG, "build")
-LIB = os.path.join(PKG, "libmrisim.so")
+OBJ = os.path.join(PKG, "build" + os.environ.get("MRISIM_LIB_SUFFIX", ""))
+# tuning builds: MRISIM_MIN_BLOCKS=<n> MRISIM_LIB_SUFFIX=_mb<n> python -m ...build  (api: MRISIM_LIB=<path>)
+_SUFFIX = os.environ.get("MRISIM_LIB_SUFFIX", "")
+LIB = os.path.join(PKG, f"libmrisim{_SUFFIX}.so")
 EXE = os.path.join(PKG, "gpu_sim.out")
 
 # -fmad=false / -ffp-contract=off: the arithmetic discipline that makes positions and
 # octree indices bit-identical to the oracle (see include/mrisim_math.h)
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
-              "-fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", INC]
+              "-fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", INC] + \
+             ([f"-DMRISIM_MIN_BLOCKS={os.environ['MRISIM_MIN_BLOCKS']}"] if os.environ.get("MRISIM_MIN_BLOCKS") else [])
 CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC]
 
 CU_SOURCES = ["mrisim.cu"]
