@@ -1,0 +1,280 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle on a B200.
+
+Bar (BASELINE.json north_star): RNG words, cell placement, octree node/leaf indices
+bit-exact; positions and T2 signal within tolerance (max |dS| / N <= 1e-6).  In the default
+EXACT field mode positions, phases, membrane flags and per-step leaf indices are bit-exact
+too; in the FAST field mode everything discrete stays bit-exact and the phases agree to
+1e-12 rad.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from mri_nanoparticle_simulation_b200 import api, dist
+
+pytestmark = pytest.mark.gpu
+
+SIGNAL_TOL = 1e-6          # max_k |S_gpu(T_k) - S_oracle(T_k)| / N   (BASELINE.json)
+FAST_PHASE_TOL = 1e-12     # rad, FAST field mode vs oracle after one sprint
+SEED = 0xC0FFEE
+TINY = dict(num_water=256, num_cells=40, bound=10, water_start_bound=6, hashDim=8, border=3)
+KATS = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scene_kats.json")))
+
+
+def make(params, seed):
+    box = api.BacteriaBox(params, seed).populateSimulation()
+    return box, ol.oracle_for_box(box, params)
+
+
+def gpu_ctx(params, box, waters, first=0, mode=api.FIELD_EXACT):
+    ctx = api.WalkerContext(params, 0)
+    ctx.set_field_mode(mode)
+    ctx.set_scene(box)
+    ctx.set_waters(waters, SEED, first)
+    return ctx
+
+
+def assert_state_equal(got, want, fields=("x", "y", "z", "phase", "in_cell", "nearest")):
+    for f in fields:
+        assert got[f].tobytes() == want[f].tobytes(), f"walker field {f} differs from the oracle"
+
+
+CASES = {
+    "tiny": (api.ParameterStruct(**TINY), 3, 3000),
+    "tiny_noavoid_lowperm": (api.low_permeability(api.ParameterStruct(avoid_intracellular_throw=0, **TINY)), 5, 3000),
+    "tiny_impermeable": (api.ParameterStruct(avoid_intracellular_throw=0, reflectIO=1.0, reflectOI=1.0, **TINY), 6, 2000),
+    "tiny_constant_kick": (api.ParameterStruct(avoid_intracellular_throw=0, kick_mode=api.KICK_CONSTANT,
+                                               phase_k=2 * 3.14 * 42 * 12 * 5e-3, **TINY), 7, 2000),
+    "default_cfg1": (api.ParameterStruct(), 12345, 2000),
+    "cfg2_noavoid_8000": (api.ParameterStruct(num_water=8000, avoid_intracellular_throw=0), 21, 1000),
+    "ragged_n": (api.ParameterStruct(**{**TINY, "num_water": 77}), 8, 2000),
+    "single_walker": (api.ParameterStruct(**{**TINY, "num_water": 1}), 9, 2000),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_traced_sprint_bit_exact(name):
+    """Every (step, walker): position, in_cell, flat leaf index; final state; RNG state."""
+    p, seed, steps = CASES[name]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    sig, tr = ctx.trace_sprint(steps)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    osig, otr = orc.run_sprint(want, wrng, 0, steps, trace=True)
+    for k in ("x", "y", "z", "in_cell", "leaf"):
+        assert np.array_equal(tr[k], otr[k]), f"{name}: per-step {k} differs"
+    assert_state_equal(ctx.get_waters(), want)
+    assert ctx.get_rng().tobytes() == wrng.tobytes()
+    assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+    assert ctx.time == steps
+    if "noavoid" in name or "impermeable" in name or "kick" in name:
+        assert tr["in_cell"].any(), "case is meant to exercise intracellular walkers"
+
+
+def test_leaf_indices_map_to_reference_subtree_offsets():
+    """flat leaf index == subtree_prefix[i] + j of the reference's (subtree i, vector offset j)."""
+    p, seed, _ = CASES["default_cfg1"]
+    box, orc = make(p, seed)
+    ctx = gpu_ctx(p, box, box.getWaters().copy())
+    _, tr = ctx.trace_sprint(1000)
+    oct_ = box.getOctree()
+    prefix = oct_.subtree_prefix
+    leaf = tr["leaf"][-1]
+    assert ((oct_.nodes["mc"][leaf] >> np.uint64(63)) == 1).all()
+    i = np.searchsorted(prefix, leaf, side="right") - 1
+    assert ((leaf - prefix[i]) < oct_.subtree_sizes[i]).all()
+    for w in range(0, len(leaf), 97):
+        idx, mc = orc.probe_leaf(tr["x"][-1, w], tr["y"][-1, w], tr["z"][-1, w])
+        assert idx == leaf[w] and mc == int(oct_.nodes["mc"][leaf[w]])
+
+
+def test_full_default_sprint_cfg1():
+    """BASELINE configs[0]: shipped parameters.h, one full sprint (20000 steps, 20 rows)."""
+    p, seed, _ = CASES["default_cfg1"]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    sig = ctx.run_sprint(p.sprintSteps)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    osig, _ = orc.run_sprint(want, wrng, 0, p.sprintSteps)
+    assert_state_equal(ctx.get_waters(), want)
+    assert ctx.get_rng().tobytes() == wrng.tobytes()
+    assert len(sig) == 20 and np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+
+
+def test_cfg3_low_permeability_100k_subsample():
+    """BASELINE configs[2] (AVOID_INTRACELLULAR_THROW + low-permeability reflectIO/OI): 100k
+    waters on the GPU, the first 4096 of them against the oracle (streams are per walker)."""
+    p = api.low_permeability(api.ParameterStruct())
+    box, orc = make(p, 12345)
+    box.rethrow_waters(100000, 4242)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    sig = ctx.run_sprint(4000)
+    got = ctx.get_waters()
+    sub, rng = w0[:4096].copy(), orc.seed(4096, SEED)
+    orc.run_sprint(sub, rng, 0, 4000)
+    assert_state_equal(got[:4096], sub)
+    assert 0.99 * len(w0) < sig[0] <= len(w0)
+
+
+def test_dense_scene_cfg4a_subsample():
+    """BASELINE configs[3] scene (2000 cells, hashDim 40, maxNeighbors 16; reference digest in
+    tests/golden/scene_kats.json): 64k walkers on the GPU, 2048 of them against the oracle."""
+    p = api.ParameterStruct(**KATS["configs"]["dense2000"])
+    box, orc = make(p, 11)
+    box.rethrow_waters(65536, 7000)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    ctx.run_sprint(2000)
+    got = ctx.get_waters()
+    sel = np.arange(0, 65536, 32)
+    sub = w0[sel].copy()
+    rng = np.concatenate([orc.seed(1, SEED, int(i)) for i in sel])
+    orc.run_sprint(sub, rng, 0, 2000)
+    assert_state_equal(got[sel], sub)
+
+
+def test_multi_sprint_with_cpmg_flip_and_resume():
+    """Sprints chain through device-resident state; flips land after sampling; a checkpoint
+    (waters + rng + time) restored into a fresh context continues bit-identically."""
+    p = api.ParameterStruct(tcp=3000, **TINY)
+    box, orc = make(p, 3)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    for k in range(4):                                   # flips at t = 3000 and 6000
+        sig = ctx.run_sprint(2000)
+        osig, _ = orc.run_sprint(want, wrng, 2000 * k, 2000)
+        assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+        assert_state_equal(ctx.get_waters(), want)
+        if k == 1:
+            ck_w, ck_r, ck_t = ctx.get_waters(), ctx.get_rng(), ctx.time
+    ctx2 = gpu_ctx(p, box, ck_w)
+    ctx2.set_rng(ck_r); ctx2.time = ck_t
+    ctx2.run_sprint(2000); ctx2.run_sprint(2000)
+    assert_state_equal(ctx2.get_waters(), want)
+
+
+def test_sharded_contexts_sum_to_unsharded():
+    """Walker sharding (dist.shard_range + first_walker_id): per-shard states concatenate to
+    the unsharded run bit-exactly; signal partials add up to it (reassociation only)."""
+    p, seed, _ = CASES["tiny_noavoid_lowperm"]
+    box, _ = make(p, seed)
+    w0 = box.getWaters().copy()
+    whole = gpu_ctx(p, box, w0)
+    s = whole.run_sprint(2000)
+    total, parts = np.zeros_like(s), []
+    for rank in range(3):
+        lo, hi = dist.shard_range(len(w0), rank, 3)
+        c = gpu_ctx(p, box, w0[lo:hi], first=lo)
+        total += c.run_sprint(2000)
+        parts.append(c.get_waters())
+    assert_state_equal(np.concatenate(parts), whole.get_waters())
+    assert np.max(np.abs(total - s)) <= 1e-12 * len(w0)
+
+
+def test_fast_field_mode_within_tolerance():
+    p, seed, _ = CASES["default_cfg1"]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0, mode=api.FIELD_FAST)
+    sig = ctx.run_sprint(p.sprintSteps)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    osig, _ = orc.run_sprint(want, wrng, 0, p.sprintSteps)
+    got = ctx.get_waters()
+    assert_state_equal(got, want, fields=("x", "y", "z", "in_cell", "nearest"))
+    assert ctx.get_rng().tobytes() == wrng.tobytes()
+    assert np.max(np.abs(got["phase"] - want["phase"])) <= FAST_PHASE_TOL
+    assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+
+
+def test_async_sprint_into_device_buffer_on_torch_stream():
+    import torch
+    p, seed, _ = CASES["tiny"]
+    box, _ = make(p, seed)
+    w0 = box.getWaters().copy()
+    a = gpu_ctx(p, box, w0)
+    ref = a.run_sprint(2000)
+    b = gpu_ctx(p, box, w0)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        out = torch.zeros(2, dtype=torch.float64, device="cuda")
+        b.run_sprint_async(2000, out.data_ptr(), st.cuda_stream)
+    st.synchronize()
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert_state_equal(b.get_waters(), a.get_waters())
+
+
+def test_size_independent_properties_1M_walkers():
+    """At bench size (1 Mi walkers, dense scene is covered by the subsample test): positions
+    in the box, membrane flag consistent with a fresh nearest-cell test, phases finite,
+    S(0+) ~ N, determinism (same inputs -> identical bits), linearity over shards."""
+    p = api.ParameterStruct(avoid_intracellular_throw=0)
+    box, orc = make(p, 12345)
+    box.rethrow_waters(1 << 20, 99)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    s1 = ctx.run_sprint(1000)
+    g1 = ctx.get_waters()
+    for k in "xyz":
+        assert (g1[k] >= 0).all() and (g1[k] < p.bound).all()
+    assert np.isfinite(g1["phase"]).all()
+    assert 0.999 * len(w0) < s1[0] <= len(w0)
+    for i in range(0, len(w0), 4099):
+        near, ic = orc.probe_nearest(g1["x"][i], g1["y"][i], g1["z"][i])
+        assert ic == g1["in_cell"][i] and near == g1["nearest"][i]
+    ctx2 = gpu_ctx(p, box, w0)
+    s2 = ctx2.run_sprint(1000)
+    assert np.array_equal(s1, s2) and ctx2.get_waters().tobytes() == g1.tobytes()
+    half = len(w0) // 2
+    a = gpu_ctx(p, box, w0[:half]); b = gpu_ctx(p, box, w0[half:], first=half)
+    assert abs((a.run_sprint(1000) + b.run_sprint(1000) - s1)[0]) <= 1e-9 * len(w0)
+
+
+def test_device_selftests_of_exact_arithmetic():
+    """The two value-exact rewrites the kernel relies on, against the IEEE operations on the
+    device: constant-divisor division and the branch-free sqrt/divide of the resident loop."""
+    L = api.lib()
+    for b in (30.0, 1.5, 0.75, 10.0, 1.25, 0.7300001):
+        assert L.mrisim_selftest_div(0, b, 50_000_000) == 0
+    assert L.mrisim_selftest_sqrt_div(0, 0.3, 2700.0, 100_000_000) == 0
+    assert L.mrisim_selftest_sqrt_div(0, 1e-3, 1e6, 100_000_000) == 0
+
+
+def test_error_paths():
+    p, seed, _ = CASES["tiny"]
+    box, _ = make(p, seed)
+    ctx = api.WalkerContext(p, 0)
+    with pytest.raises(api.MrisimError, match="scene incomplete|no waters"):
+        ctx.run_sprint(1000)
+    ctx.set_scene(box)
+    with pytest.raises(api.MrisimError, match="no waters"):
+        ctx.run_sprint(1000)
+    ctx.set_waters(box.getWaters().copy(), SEED)
+    with pytest.raises(api.MrisimError, match="multiple of pfreq"):
+        ctx.run_sprint(1500)
+    with pytest.raises(api.MrisimError):
+        api.WalkerContext(p, 99)
+    assert ctx.kernel_launches >= 1
+
+
+def test_simulate_waters_dropin_csv(tmp_path):
+    """mrisim_simulate_waters == simulateWaters(fName): CSV rows `time*tau,signal` with the
+    reference's ostream formatting, equal to the oracle's rows at 6 significant digits."""
+    p = api.ParameterStruct(sprintSteps=2000, **TINY)
+    out = str(tmp_path / "signal.csv")
+    api.simulateWaters(out, p, host_seed=3, walker_seed=SEED, device=0, max_sprints=2)
+    rows = open(out).read().splitlines()
+    assert len(rows) == 4
+    box, orc = make(p, 3)
+    w, rng = box.getWaters().copy(), orc.seed(p.num_water, SEED)
+    want = np.concatenate([orc.run_sprint(w, rng, 2000 * k, 2000)[0] for k in range(2)])
+    for k, line in enumerate(rows):
+        assert line == api.csv_row(1000 * (k + 1), p.tau, want[k]).rstrip("\n")
+    assert rows[0].startswith("0.001,")
