@@ -57,7 +57,7 @@ def _run(cmd, verbose):
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile every source for sm_100a and link libmrisim.so; returns its path."""
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(INC, f) for f in os.listdir(INC)] + \
+    headers = [os.path.join(INC, f) for f in os.listdir(INC) if os.path.isfile(os.path.join(INC, f))] + \
               [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h")]
     sources = [os.path.join(CSRC, f) for f in CU_SOURCES + CXX_SOURCES if os.path.exists(os.path.join(CSRC, f))]
     stamp = os.path.join(OBJ, "stamp")
