@@ -1,0 +1,23 @@
+#!/bin/bash
+# One GPU-box visit: parity suite, bench, launch list, full ncu capture of the hot kernel.
+#   gpurun --timeout 1800 -- 'bash scripts/gpu_round.sh <tag>'
+set -u
+cd "$(dirname "$0")/.."
+tag=${1:-run}
+out=gpurun_out/$tag
+mkdir -p $out
+nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $out/gpu.txt 2>&1
+(time python -m pytest tests -m gpu -x -q) > $out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a $out/pytest_gpu.log
+python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
+cat $out/bench.json
+python bench.py --field-mode fast --no-cpu-baseline --steps 3 > $out/bench_fast.json 2>> $out/bench.err
+if [ "${NCU:-1}" = "1" ]; then
+python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $out/plain_bench.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $out/launches.csv \
+    python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $out/ncu_launches.log 2>&1
+python scripts/profile_case.py 1048576 1000 1 > $out/plain_profile_case.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:walker_sprint -s 1 -c 1 -o $out/prof \
+    python scripts/profile_case.py 1048576 1000 1 > $out/ncu_full.log 2>&1
+cat $out/plain_profile_case.log
+fi
+tail -3 $out/pytest_gpu.log
