@@ -154,6 +154,13 @@ int  mrisim_create(const mrisim_params* p, int device, mrisim_ctx** out);
 void mrisim_destroy(mrisim_ctx* ctx);                 /* finalizeGPU (cuda_sim.cu:430-433) */
 const char* mrisim_last_error(const mrisim_ctx* ctx); /* ctx may be NULL: last create error */
 int  mrisim_set_field_mode(mrisim_ctx* ctx, int mode);
+/* Launch granularity of a sprint (no reference analogue; the reference launches one kernel per
+ * sprint, cuda_sim.cu:980).  A sprint is cut into launches of `steps` timesteps; between launches
+ * the walkers are re-ordered by the octree leaf they sit in so that the lanes of a warp share
+ * resident lists and lookup rows.  Results per walker are unaffected (state and random stream
+ * travel with the walker index); only the association order of the signal sum changes.
+ * steps < 0: default (pfreq); steps == 0: one launch per sprint, walkers in array order. */
+int  mrisim_set_resort_steps(mrisim_ctx* ctx, int32_t steps);
 
 /* `p_array<Triple> dev_lattice(p.num_cells, simBox.getCells(), d.lattice)` (cuda_sim.cu:935,960) */
 int  mrisim_set_cells(mrisim_ctx* ctx, const double* xyz, int32_t num_cells);

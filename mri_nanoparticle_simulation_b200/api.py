@@ -60,6 +60,7 @@ def lib():
         "mrisim_destroy": (None, [vp]),
         "mrisim_last_error": (C.c_char_p, [vp]),
         "mrisim_set_field_mode": (C.c_int, [vp, C.c_int]),
+        "mrisim_set_resort_steps": (C.c_int, [vp, i32]),
         "mrisim_set_cells": (C.c_int, [vp, vp, i32]),
         "mrisim_set_lookup": (C.c_int, [vp, vp, i32, i32]),
         "mrisim_set_octree": (C.c_int, [vp, i32, i32, vp, i32, vp, u64, vp, u64]),
@@ -95,7 +96,7 @@ ABI_SYMBOLS = [
     "mrisim_scene_build", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters",
-    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode",
+    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_resort_steps",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
@@ -245,6 +246,11 @@ class WalkerContext:
 
     def set_field_mode(self, mode: int):
         self._ck(lib().mrisim_set_field_mode(self._h, mode))
+
+    def set_resort_steps(self, steps: int):
+        """Steps per kernel launch; walkers are re-ordered by octree leaf between launches
+        (<0: default = pfreq, 0: one launch per sprint in array order)."""
+        self._ck(lib().mrisim_set_resort_steps(self._h, steps))
 
     def set_scene(self, box: BacteriaBox):
         self._ck(lib().mrisim_set_scene(self._h, box._handle()))
