@@ -236,6 +236,11 @@ int64_t mrisim_selftest_div(int device, double b, uint64_t n);
  * [lo, hi] (sqrt(x), t/(x*x*sqrt(x)), t/x against the compiler's IEEE sqrt and divide). */
 int64_t mrisim_selftest_sqrt_div(int device, double lo, double hi, uint64_t n);
 
+/* Same for the integer fast paths of the Morton word floor(x/bound*2^21) (cuda_sim.cu:129-135) and
+ * of the lookup-lattice coordinate int(x/cubeLength) (cuda_sim.cu:455-457): 15n coordinates in
+ * [0, bound), random and on both sides of every boundary, against the IEEE-divide expressions. */
+int64_t mrisim_selftest_index(int device, double bound, int32_t hashDim, uint64_t n);
+
 int mrisim_version(void);
 
 #ifdef __cplusplus

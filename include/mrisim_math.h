@@ -106,15 +106,48 @@ MRISIM_HD double mrisim_u01_from_bits(uint64_t x) {
 }
 MRISIM_HD double mrisim_rng_u01(mrisim_rng* r) { return mrisim_u01_from_bits(mrisim_rng_next(r)); }
 
+/* Polynomial coefficients.  On the device they are read from the constant bank (one operand of
+ * the DFMA) instead of being materialised into registers as immediates, two moves per
+ * coefficient; the VALUES are the same literals either way. */
+#define MRISIM_LG1 6.666666666666735130e-01
+#define MRISIM_LG2 3.999999999940941908e-01
+#define MRISIM_LG3 2.857142874366239149e-01
+#define MRISIM_LG4 2.222219843214978396e-01
+#define MRISIM_LG5 1.818357216161805012e-01
+#define MRISIM_LG6 1.531383769920937332e-01
+#define MRISIM_LG7 1.479819860511658591e-01
+#define MRISIM_S1 -1.66666666666666324348e-01
+#define MRISIM_S2 8.33333333332248946124e-03
+#define MRISIM_S3 -1.98412698298579493134e-04
+#define MRISIM_S4 2.75573137070700676789e-06
+#define MRISIM_S5 -2.50507602534068634195e-08
+#define MRISIM_S6 1.58969099521155010221e-10
+#define MRISIM_C1 4.16666666666666019037e-02
+#define MRISIM_C2 -1.38888888888741095749e-03
+#define MRISIM_C3 2.48015872894767294178e-05
+#define MRISIM_C4 -2.75573143513906633035e-07
+#define MRISIM_C5 2.08757232129817482790e-09
+#define MRISIM_C6 -1.13596475577881948265e-11
+#if defined(__CUDACC__)
+static __constant__ double mrisim_kc[19] = {
+    MRISIM_LG1, MRISIM_LG2, MRISIM_LG3, MRISIM_LG4, MRISIM_LG5, MRISIM_LG6, MRISIM_LG7,
+    MRISIM_S1, MRISIM_S2, MRISIM_S3, MRISIM_S4, MRISIM_S5, MRISIM_S6,
+    MRISIM_C1, MRISIM_C2, MRISIM_C3, MRISIM_C4, MRISIM_C5, MRISIM_C6};
+#endif
+#if defined(__CUDA_ARCH__)
+#define MRISIM_KC(i, lit) mrisim_kc[i]
+#else
+#define MRISIM_KC(i, lit) (lit)
+#endif
+
 /* ---- ln(v) for v in [2^-52, 1] ------------------------------------------------------ */
 /* v = 2^k * m, m in [sqrt(1/2), sqrt(2)); f = m - 1; s = f/(2+f); ln m = f - f^2/2 + s*(f^2/2 + R(s^2)). */
 MRISIM_HD double mrisim_log(double v) {
     const double ln2_hi = 6.93147180369123816490e-01;   /* 0x3fe62e42fee00000 */
     const double ln2_lo = 1.90821492927058770002e-10;   /* 0x3dea39ef35793c76 */
-    const double Lg1 = 6.666666666666735130e-01, Lg2 = 3.999999999940941908e-01,
-                 Lg3 = 2.857142874366239149e-01, Lg4 = 2.222219843214978396e-01,
-                 Lg5 = 1.818357216161805012e-01, Lg6 = 1.531383769920937332e-01,
-                 Lg7 = 1.479819860511658591e-01;
+    const double Lg1 = MRISIM_KC(0, MRISIM_LG1), Lg2 = MRISIM_KC(1, MRISIM_LG2), Lg3 = MRISIM_KC(2, MRISIM_LG3),
+                 Lg4 = MRISIM_KC(3, MRISIM_LG4), Lg5 = MRISIM_KC(4, MRISIM_LG5), Lg6 = MRISIM_KC(5, MRISIM_LG6),
+                 Lg7 = MRISIM_KC(6, MRISIM_LG7);
     uint64_t b = mrisim_double_to_bits(v);
     int32_t k = (int32_t)(b >> 52) - 1023;               /* v is normal and positive */
     uint64_t mant = b & UINT64_C(0x000FFFFFFFFFFFFF);
@@ -141,12 +174,10 @@ MRISIM_HD double mrisim_log(double v) {
  * theta = f*pi/2 in [-pi/4, pi/4]; odd/even minimax kernels; quadrant fix-up. */
 MRISIM_HD void mrisim_sincos2pi(double u, double* sn, double* cs) {
     const double pio2 = 1.57079632679489655800e+00;
-    const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
-                 S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
-                 S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
-    const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
-                 C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
-                 C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+    const double S1 = MRISIM_KC(7, MRISIM_S1), S2 = MRISIM_KC(8, MRISIM_S2), S3 = MRISIM_KC(9, MRISIM_S3),
+                 S4 = MRISIM_KC(10, MRISIM_S4), S5 = MRISIM_KC(11, MRISIM_S5), S6 = MRISIM_KC(12, MRISIM_S6);
+    const double C1 = MRISIM_KC(13, MRISIM_C1), C2 = MRISIM_KC(14, MRISIM_C2), C3 = MRISIM_KC(15, MRISIM_C3),
+                 C4 = MRISIM_KC(16, MRISIM_C4), C5 = MRISIM_KC(17, MRISIM_C5), C6 = MRISIM_KC(18, MRISIM_C6);
     const double r = u * 4.0;
     const int32_t n = (int32_t)(r + 0.5);
     const double f = r - (double)n;
@@ -156,22 +187,22 @@ MRISIM_HD void mrisim_sincos2pi(double u, double* sn, double* cs) {
     const double s = mrisim_fma(z * th, ps, th);
     const double pc = mrisim_fma(z, mrisim_fma(z, mrisim_fma(z, mrisim_fma(z, mrisim_fma(z, C6, C5), C4), C3), C2), C1);
     const double c = mrisim_fma(z * z, pc, mrisim_fma(z, -0.5, 1.0));
-    switch (n & 3) {
-        case 0:  *sn = s;  *cs = c;  break;
-        case 1:  *sn = c;  *cs = -s; break;
-        case 2:  *sn = -s; *cs = -c; break;
-        default: *sn = -c; *cs = s;  break;
-    }
+    /* quadrant fix-up, branch-free: n&3 = 0: (s, c)  1: (c, -s)  2: (-s, -c)  3: (-c, s) */
+    const double a = (n & 1) ? c : s, b = (n & 1) ? s : c;
+    *sn = (n & 2) ? -a : a;
+    *cs = ((n + 1) & 2) ? -b : b;
 }
 
 /* ---- Box-Muller pair from two [0,1) uniforms ---------------------------------------- */
-MRISIM_HD void mrisim_normal_pair(double u1, double u2, double* z0, double* z1) {
-    const double v = 1.0 - u1;                           /* exact, in (0,1] */
+MRISIM_HD void mrisim_normal_pair_v(double v, double u2, double* z0, double* z1) {   /* v = 1 - u1 */
     const double r = mrisim_sqrt(-2.0 * mrisim_log(v));
     double s, c;
     mrisim_sincos2pi(u2, &s, &c);
     *z0 = r * c;
     *z1 = r * s;
+}
+MRISIM_HD void mrisim_normal_pair(double u1, double u2, double* z0, double* z1) {
+    mrisim_normal_pair_v(1.0 - u1, u2, z0, z1);          /* exact, in (0,1] */
 }
 
 /* ---- the intracellular kick of cuda_sim.cu:632, in closed form ---------------------- */

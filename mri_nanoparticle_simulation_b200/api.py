@@ -81,6 +81,7 @@ def lib():
         "mrisim_measure_fp64_tflops": (dbl, [C.c_int, C.c_int]),
         "mrisim_selftest_div": (i64, [C.c_int, dbl, u64]),
         "mrisim_selftest_sqrt_div": (i64, [C.c_int, dbl, dbl, u64]),
+        "mrisim_selftest_index": (i64, [C.c_int, dbl, i32, u64]),
         "mrisim_simulate_waters": (C.c_int, [C.c_char_p, PP, u64, u64, C.c_int, i64]),
     }
     for name, (res, args) in sig.items():
@@ -101,7 +102,7 @@ ABI_SYMBOLS = [
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
-    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div",
+    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index",
 ]
 
 
