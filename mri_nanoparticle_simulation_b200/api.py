@@ -61,6 +61,7 @@ def lib():
         "mrisim_last_error": (C.c_char_p, [vp]),
         "mrisim_set_field_mode": (C.c_int, [vp, C.c_int]),
         "mrisim_set_resort_steps": (C.c_int, [vp, i32]),
+        "mrisim_set_overlap_groups": (C.c_int, [vp, i32]),
         "mrisim_set_cells": (C.c_int, [vp, vp, i32]),
         "mrisim_set_lookup": (C.c_int, [vp, vp, i32, i32]),
         "mrisim_set_octree": (C.c_int, [vp, i32, i32, vp, i32, vp, u64, vp, u64]),
@@ -97,7 +98,7 @@ ABI_SYMBOLS = [
     "mrisim_scene_build", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters",
-    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_resort_steps",
+    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
@@ -250,8 +251,12 @@ class WalkerContext:
 
     def set_resort_steps(self, steps: int):
         """Steps per kernel launch; walkers are re-ordered by octree leaf between launches
-        (<0: default = pfreq, 0: one launch per sprint in array order)."""
+        (<0: default = 250, 0: one launch per sprint in array order)."""
         self._ck(lib().mrisim_set_resort_steps(self._h, steps))
+
+    def set_overlap_groups(self, groups: int):
+        """Walker ranges whose launch chains overlap on separate streams (default 1)."""
+        self._ck(lib().mrisim_set_overlap_groups(self._h, groups))
 
     def set_scene(self, box: BacteriaBox):
         self._ck(lib().mrisim_set_scene(self._h, box._handle()))

@@ -76,6 +76,49 @@ def test_traced_sprint_bit_exact(name):
         assert tr["in_cell"].any(), "case is meant to exercise intracellular walkers"
 
 
+@pytest.mark.parametrize("resort,groups", [(0, 1), (300, 1), (1000, 2), (70, 3)])
+def test_launch_granularity_and_overlap_groups_do_not_change_walkers(resort, groups):
+    """A sprint cut into launches of any length (block sums carried across launches), walkers
+    re-ordered by leaf in between, the walker array split into overlapping launch chains: every
+    walker's state is the oracle's bit for bit; the signal differs by reassociation only."""
+    p = api.low_permeability(api.ParameterStruct(num_cells=60, bound=12, water_start_bound=8, hashDim=10, border=3,
+                                                  avoid_intracellular_throw=0, num_water=64))
+    box, orc = make(p, 17)
+    box.rethrow_waters(80000, 31)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    ctx.set_resort_steps(resort); ctx.set_overlap_groups(groups)
+    sig = np.concatenate([ctx.run_sprint(2000), ctx.run_sprint(1000)])
+    got, grng = ctx.get_waters(), ctx.get_rng()
+    sel = np.arange(0, len(w0), 41)
+    sub = w0[sel].copy()
+    rng = np.concatenate([orc.seed(1, SEED, int(i)) for i in sel])
+    orc.run_sprint(sub, rng, 0, 2000); orc.run_sprint(sub, rng, 2000, 1000)
+    assert_state_equal(got[sel], sub)
+    assert grng[sel].tobytes() == rng.tobytes()
+    ref = gpu_ctx(p, box, w0)
+    ref.set_resort_steps(0); ref.set_overlap_groups(1)
+    rsig = np.concatenate([ref.run_sprint(2000), ref.run_sprint(1000)])
+    assert ref.get_waters().tobytes() == got.tobytes()
+    assert np.max(np.abs(sig - rsig)) <= 1e-9 * len(w0)
+
+
+def test_traced_sprint_with_short_launches():
+    """Per-step trace (positions, flags, leaf indices) with 130-step launches and re-ordering."""
+    p, seed, _ = CASES["tiny_noavoid_lowperm"]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    ctx.set_resort_steps(130)
+    sig, tr = ctx.trace_sprint(2000)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    osig, otr = orc.run_sprint(want, wrng, 0, 2000, trace=True)
+    for k in ("x", "y", "z", "in_cell", "leaf"):
+        assert np.array_equal(tr[k], otr[k]), f"per-step {k} differs"
+    assert_state_equal(ctx.get_waters(), want)
+    assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+
+
 def test_leaf_indices_map_to_reference_subtree_offsets():
     """flat leaf index == subtree_prefix[i] + j of the reference's (subtree i, vector offset j)."""
     p, seed, _ = CASES["default_cfg1"]
