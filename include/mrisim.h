@@ -159,7 +159,7 @@ int  mrisim_set_field_mode(mrisim_ctx* ctx, int mode);
  * the walkers are re-ordered by the octree leaf they sit in so that the lanes of a warp share
  * resident lists and lookup rows.  Results per walker are unaffected (state and random stream
  * travel with the walker index); only the association order of the signal sum changes.
- * steps < 0: default (250); steps == 0: one launch per sprint, walkers in array order. */
+ * steps < 0: default (125); steps == 0: one launch per sprint, walkers in array order. */
 int  mrisim_set_resort_steps(mrisim_ctx* ctx, int32_t steps);
 /* The walker array is cut into `groups` contiguous ranges whose launch chains run on separate
  * streams, so that the tail of one range's kernel overlaps the body of another's (default 1 = a

@@ -251,7 +251,7 @@ class WalkerContext:
 
     def set_resort_steps(self, steps: int):
         """Steps per kernel launch; walkers are re-ordered by octree leaf between launches
-        (<0: default = 250, 0: one launch per sprint in array order)."""
+        (<0: default = 125, 0: one launch per sprint in array order)."""
         self._ck(lib().mrisim_set_resort_steps(self._h, steps))
 
     def set_overlap_groups(self, groups: int):

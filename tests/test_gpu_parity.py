@@ -288,6 +288,7 @@ def test_device_selftests_of_exact_arithmetic():
         assert L.mrisim_selftest_div(0, b, 50_000_000) == 0
     assert L.mrisim_selftest_sqrt_div(0, 0.3, 2700.0, 100_000_000) == 0
     assert L.mrisim_selftest_sqrt_div(0, 1e-3, 1e6, 100_000_000) == 0
+    assert L.mrisim_selftest_sqrt_div(0, 1e-31, 4.0, 100_000_000) == 0      # |d|^2 of the displacement
     # integer fast paths of the Morton word and the lookup-lattice coordinate
     for bound, h in ((30.0, 20), (30.0, 40), (10.0, 8), (7.3, 1290), (100.0, 3)):
         assert L.mrisim_selftest_index(0, bound, h, 20_000_000) == 0
