@@ -4,7 +4,7 @@ import collections, csv, io, re, subprocess, sys
 rep, N = sys.argv[1], float(sys.argv[2])
 txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
 lines = collections.defaultdict(lambda: [0, 0, 0, ""]); ops = collections.Counter(); opthr = collections.Counter()
-fname = None; hdr = None
+fname = None; hdr = None; seen = set(); cur = None
 for row in csv.reader(io.StringIO(txt)):
     if not row: continue
     if row[0] == "File Path": fname = row[1].split("/")[-1]; hdr = None; continue
@@ -13,9 +13,12 @@ for row in csv.reader(io.StringIO(txt)):
     if hdr is None or len(row) <= ism: continue
     try: e = int(row[ie]); t = int(row[it]); s = int(row[ism])
     except ValueError: continue
-    if row[0] != "":                       # aggregate row of one source line
-        L = lines[(fname, int(row[0]))]; L[0] += e; L[1] += t; L[2] += s; L[3] = row[1].strip()[:90]
-    else:                                  # one SASS instruction attributed to that line
+    if row[0] != "":                       # aggregate row of one source line (its totals double-count inlined code)
+        cur = lines[(fname, int(row[0]))]; cur[3] = row[1].strip()[:90]
+    else:                                  # one SASS instruction attributed to that line; charged once
+        if row[2] in seen: continue
+        seen.add(row[2])
+        cur[0] += e; cur[1] += t; cur[2] += s
         m = re.match(r"\s*(@!?U?P\d+\s+)?([A-Z0-9_]+)", row[3]); op = m.group(2) if m else "?"
         ops[op] += e; opthr[op] += t
 T = sum(v[0] for v in lines.values()); S = sum(v[2] for v in lines.values())
