@@ -325,13 +325,34 @@ def main():
     F = algorithmic_ops(Cbar, Lbar, Rbar)
     k_ms = float(np.mean(kernel_ms))
     achieved = n_per_gpu * steps * F / (k_ms * 1e-3) / 1e12
-    traffic = None
-    prof = os.path.join(ROOT, "profiles", "traffic_r01.json")
-    if os.path.exists(prof):
+    traffic = None                      # DRAM bytes of one walker-kernel launch (ncu --set full capture of the same launch shape)
+    prof = os.path.join(ROOT, "profiles", "instr_mix_r01.json")
+    if os.path.exists(prof) and args.field_mode == "exact" and args.workload == DEFAULT_WORKLOAD and not args.walkers_per_gpu:
         try:
             traffic = json.load(open(prof)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
+    # Issue-slot view: on B200 an FP64 warp instruction holds the SMSP issue port for
+    # two cycles, so the binding resource is issue slots = 2 x FP64 + other instructions.  The
+    # instruction mix per warp-step comes from the committed ncu capture of this kernel; the rate
+    # and the clock are measured live.
+    issue = None
+    mixf = os.path.join(ROOT, "profiles", "instr_mix_r01.json")
+    if os.path.exists(mixf) and args.field_mode == "exact" and clocks and clocks.get("sm_mhz"):
+        try:
+            mix = json.load(open(mixf))
+            n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+            warp_steps_per_s = n_per_gpu / 32.0 * steps / (k_ms * 1e-3)
+            cyc_per_s = n_sm * 4 * clocks["sm_mhz"] * 1e6
+            issue = {"fp64_inst_per_warp_step": mix["fp64_inst_per_warp_step"], "other_inst_per_warp_step": mix["other_inst_per_warp_step"],
+                     "issue_slots_per_warp_step": mix["issue_slots_per_warp_step"],
+                     "issue_slot_frac": mix["issue_slots_per_warp_step"] * warp_steps_per_s / cyc_per_s,
+                     "fp64_pipe_frac": 2 * mix["fp64_inst_per_warp_step"] * warp_steps_per_s / cyc_per_s,
+                     "instr_mix_from": "profiles/" + str(mix.get("source", "instr_mix_r01.json")) + " (" + str(mix.get("tag")) + ")",
+                     "note": "issue slots = 2*FP64 + other warp instructions (an FP64 instruction holds the SMSP issue port for 2 cycles, "
+                             "profiles/fp64_issue_probe_r01.txt); frac = slots issued per SMSP cycle at the sampled SM clock"}
+        except Exception as e:      # a stale or missing profile only removes the extra view
+            issue = {"error": str(e)}
     line = {
         "metric": "walker-steps/sec", "value": value, "unit": "walker-steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
@@ -347,7 +368,7 @@ def main():
         "clocks": clocks,
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
                      "traffic": traffic, "kernel": "walker_sprint_kernel", "kernel_ms": k_ms,
-                     "algorithmic_fp64_ops_per_walker_step": F, "C_L_R": [Cbar, Lbar, Rbar],
+                     "algorithmic_fp64_ops_per_walker_step": F, "C_L_R": [Cbar, Lbar, Rbar], "issue": issue,
                      "peak_source": "measured live: mrisim_measure_fp64_tflops (8 independent DFMA chains/thread, all SMs); "
                                     "MEASURED_PEAKS.json has no FP64 entry",
                      "note": "path is FP64-pipe bound, not HBM/tensor (SURVEY.md 8d): per-step HBM traffic is ~0"},

@@ -24,7 +24,22 @@ for v in rows[2:]:
         if "issue_stalled" in k and k.endswith("per_issue_active.ratio") and "not_issued" not in k:
             m["stall_" + k.split("issue_stalled_")[1].replace("_per_issue_active.ratio", "")] = v[i]
     if "smsp__inst_executed.sum" in m:
-        m["warp_instructions_per_warp_step"] = float(m["smsp__inst_executed.sum"][0]) / warp_steps
+        tot = float(m["smsp__inst_executed.sum"][0]) / warp_steps
+        m["warp_instructions_per_warp_step"] = tot
+        # FP64-pipe warp instructions: the pipe takes one per two cycles per SMSP, i.e. 2 per cycle per SM
+        n_sm = 148
+        f = float(m["sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active"][0]) / 100 * 2 * float(m["sm__cycles_active.avg"][0]) * n_sm / warp_steps
+        cyc = float(m["sm__cycles_elapsed.avg"][0]) * n_sm * 4 / warp_steps
+        m["issue_model"] = {"fp64_inst_per_warp_step": f, "other_inst_per_warp_step": tot - f,
+                            "issue_slots_per_warp_step": tot + f, "smsp_cycles_per_warp_step": cyc,
+                            "issue_slot_frac": (tot + f) / cyc, "fp64_pipe_frac": 2 * f / cyc,
+                            "note": "an FP64 warp instruction holds the SMSP issue port for 2 cycles on B200 (profiles/fp64_issue_probe_r01.txt): slots = 2*fp64 + other"}
+        def mb(k):
+            v, unit = m[k]
+            return float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+        json.dump({"source": os.path.basename(rep), "tag": tag, "what": what,
+                   "dram_bytes_per_launch": mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), **m["issue_model"]},
+                  open(os.path.join(ROOT, "profiles", "instr_mix_r01.json"), "w"), indent=1)
     out["launches"].append(m)
 json.dump(out, open(os.path.join(ROOT, "profiles", f"ncu_r01_{tag}_summary.json"), "w"), indent=1)
 lines = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "ncu_lines.py"), rep, str(warp_steps), "70"],

@@ -308,6 +308,10 @@ def test_error_paths():
         ctx.run_sprint(1500)
     with pytest.raises(api.MrisimError):
         api.WalkerContext(p, 99)
+    bad = box.getWaters().copy()
+    bad["x"][0] = -1e-9                       # the reference would index its lookup table out of bounds
+    with pytest.raises(api.MrisimError, match="outside the periodic box"):
+        ctx.set_waters(bad, SEED)
     assert ctx.kernel_launches >= 1
 
 
