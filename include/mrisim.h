@@ -149,11 +149,27 @@ enum {
     MRISIM_FIELD_FAST  = 1      /* rsqrt/FMA form: same positions/indices, phase within 1e-12 */
 };
 
+/* How a sprint is mapped onto the GPU.  Per-walker results (positions, flags, leaf indices, RNG
+ * state, phases) are bit-identical in both; only the association order of the signal sum differs.
+ *   FUSED    one thread per walker, the whole step in registers (many walkers: issue-bound).
+ *   PIPELINE the reference's own split (cuda_sim.cu:976-1013: draws, diffusion, phase accumulation,
+ *            block sum), for FEW walkers where one thread per walker leaves the GPU latency-bound:
+ *            draws per (walker, chunk) from GF(2) jump-ahead states, a serial position kernel, the
+ *            field per (walker, step), ordered block sums.  Needs even pfreq and whole intervals.
+ *   AUTO     PIPELINE up to 49 152 walkers, FUSED above (default). */
+enum {
+    MRISIM_PATH_AUTO = 0,
+    MRISIM_PATH_FUSED = 1,
+    MRISIM_PATH_PIPELINE = 2
+};
+
 /* initGPUParams (cuda_sim.cu:406-408) + `Handler handle(0)` (:916). */
 int  mrisim_create(const mrisim_params* p, int device, mrisim_ctx** out);
 void mrisim_destroy(mrisim_ctx* ctx);                 /* finalizeGPU (cuda_sim.cu:430-433) */
 const char* mrisim_last_error(const mrisim_ctx* ctx); /* ctx may be NULL: last create error */
 int  mrisim_set_field_mode(mrisim_ctx* ctx, int mode);
+int  mrisim_set_path_mode(mrisim_ctx* ctx, int mode);
+uint64_t mrisim_pipeline_sprints(const mrisim_ctx* ctx);   /* sprints that took the PIPELINE path */
 /* Launch granularity of a sprint (no reference analogue; the reference launches one kernel per
  * sprint, cuda_sim.cu:980).  A sprint is cut into launches of `steps` timesteps; between launches
  * the walkers are re-ordered by the octree leaf they sit in so that the lanes of a warp share

@@ -7,6 +7,7 @@ import numpy as np
 
 KICK_NONE, KICK_RANDOM, KICK_CONSTANT = 0, 1, 2
 FIELD_EXACT, FIELD_FAST = 0, 1
+PATH_AUTO, PATH_FUSED, PATH_PIPELINE = 0, 1, 2     # include/mrisim.h
 
 
 class Params(C.Structure):

@@ -16,7 +16,7 @@ from typing import Optional
 import numpy as np
 
 from . import _cabi as cabi
-from ._cabi import FIELD_EXACT, FIELD_FAST, KICK_CONSTANT, KICK_NONE, KICK_RANDOM, Params  # noqa: F401
+from ._cabi import FIELD_EXACT, FIELD_FAST, PATH_AUTO, PATH_FUSED, PATH_PIPELINE, KICK_CONSTANT, KICK_NONE, KICK_RANDOM, Params  # noqa: F401
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MRISIM_LIB") or os.path.join(PKG, "libmrisim.so")   # MRISIM_LIB: tuning builds only
@@ -60,6 +60,8 @@ def lib():
         "mrisim_destroy": (None, [vp]),
         "mrisim_last_error": (C.c_char_p, [vp]),
         "mrisim_set_field_mode": (C.c_int, [vp, C.c_int]),
+        "mrisim_set_path_mode": (C.c_int, [vp, C.c_int]),
+        "mrisim_pipeline_sprints": (C.c_uint64, [vp]),
         "mrisim_set_resort_steps": (C.c_int, [vp, i32]),
         "mrisim_set_overlap_groups": (C.c_int, [vp, i32]),
         "mrisim_set_cells": (C.c_int, [vp, vp, i32]),
@@ -98,7 +100,7 @@ ABI_SYMBOLS = [
     "mrisim_scene_build", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters",
-    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
+    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
@@ -248,6 +250,14 @@ class WalkerContext:
 
     def set_field_mode(self, mode: int):
         self._ck(lib().mrisim_set_field_mode(self._h, mode))
+
+    def set_path_mode(self, mode: int):
+        """PATH_AUTO (default) / PATH_FUSED / PATH_PIPELINE, see include/mrisim.h."""
+        self._ck(lib().mrisim_set_path_mode(self._h, mode))
+
+    @property
+    def pipeline_sprints(self) -> int:
+        return int(lib().mrisim_pipeline_sprints(self._h))
 
     def set_resort_steps(self, steps: int):
         """Steps per kernel launch; walkers are re-ordered by octree leaf between launches

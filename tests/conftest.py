@@ -11,6 +11,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "slow: minutes of GPU time (deselect with -m 'gpu and not slow' while iterating)")
 
 
 @pytest.fixture(scope="session", autouse=True)

@@ -76,6 +76,60 @@ def test_traced_sprint_bit_exact(name):
         assert tr["in_cell"].any(), "case is meant to exercise intracellular walkers"
 
 
+@pytest.mark.parametrize("name", sorted(CASES))
+@pytest.mark.parametrize("field_mode", [api.FIELD_EXACT, api.FIELD_FAST])
+def test_pipelined_path_bit_exact(name, field_mode):
+    """The few-walker PIPELINE path (jump-ahead draws, serial position kernel, per-step field, ordered
+    block sums) against the oracle over two chained sprints: final walkers, RNG state incl. the spare
+    normal, signal; and against the FUSED path, whose walkers it must equal bit for bit."""
+    p, seed, _ = CASES[name]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0, mode=field_mode)
+    ctx.set_path_mode(api.PATH_PIPELINE)
+    sig = np.concatenate([ctx.run_sprint(2000), ctx.run_sprint(1000)])
+    assert ctx.pipeline_sprints == 2 and ctx.time == 3000
+    fused = gpu_ctx(p, box, w0, mode=field_mode)
+    fused.set_path_mode(api.PATH_FUSED)
+    fsig = np.concatenate([fused.run_sprint(2000), fused.run_sprint(1000)])
+    assert fused.pipeline_sprints == 0
+    got, grng = ctx.get_waters(), ctx.get_rng()
+    assert got.tobytes() == fused.get_waters().tobytes() and grng.tobytes() == fused.get_rng().tobytes()
+    assert np.max(np.abs(sig - fsig)) <= 1e-9 * len(w0)
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    osig = np.concatenate([orc.run_sprint(want, wrng, 0, 2000)[0], orc.run_sprint(want, wrng, 2000, 1000)[0]])
+    assert grng.tobytes() == wrng.tobytes()
+    if field_mode == api.FIELD_EXACT:
+        assert_state_equal(got, want)
+    else:
+        assert_state_equal(got, want, fields=("x", "y", "z", "in_cell", "nearest"))
+        assert np.max(np.abs(got["phase"] - want["phase"])) <= FAST_PHASE_TOL
+    assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
+
+
+def test_path_mode_auto_and_fallbacks():
+    """AUTO takes the pipelined path for few walkers and the fused one for many, for traces, and for
+    sprints that do not start on an even step; mixing the paths sprint by sprint changes no walker."""
+    p, seed, _ = CASES["tiny_noavoid_lowperm"]
+    box, orc = make(p, seed)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    ctx.run_sprint(1000)
+    assert ctx.pipeline_sprints == 1
+    ctx.trace_sprint(1000)                                   # traces use the fused kernel
+    assert ctx.pipeline_sprints == 1
+    ctx.set_path_mode(api.PATH_FUSED); ctx.run_sprint(1000)
+    ctx.set_path_mode(api.PATH_AUTO); ctx.run_sprint(2000)
+    assert ctx.pipeline_sprints == 2
+    want, wrng = w0.copy(), orc.seed(len(w0), SEED)
+    for t0, n in ((0, 1000), (1000, 1000), (2000, 1000), (3000, 2000)):
+        orc.run_sprint(want, wrng, t0, n)
+    assert_state_equal(ctx.get_waters(), want)
+    assert ctx.get_rng().tobytes() == wrng.tobytes()
+    with pytest.raises(api.MrisimError, match="unknown mode"):
+        ctx.set_path_mode(7)
+
+
 @pytest.mark.parametrize("resort,groups", [(0, 1), (300, 1), (1000, 2), (70, 3)])
 def test_launch_granularity_and_overlap_groups_do_not_change_walkers(resort, groups):
     """A sprint cut into launches of any length (block sums carried across launches), walkers

@@ -1,0 +1,70 @@
+"""Statistical cross-check of the walk against the reference's OWN GPU code run on this box.
+
+oracle/_ref/ref_gpu_xcheck is the reference's cuda_sim.cu + gpu_random.cu + host sources,
+compiled where they lie (`make -C oracle refgpu`; the missing utilities/ submodule is replaced by
+oracle/shim/utilities/utilities.h, the wall-clock scene seed by -DREF_HOST_SEED=12345).  Its
+walker randomness is cuRAND XORWOW seeded from the clock, ours is the per-walker xoroshiro128+
+contract: the two runs share the scene (our host builder is byte-identical to the reference's)
+and the physics, not the random numbers, so the T2 signals must agree within Monte-Carlo error.
+This is what pins the step loop (diffusion step, membrane, octree field, phase, CPMG flip) to the
+reference beyond the CPU restatement in oracle/walk_oracle.c.
+"""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from mri_nanoparticle_simulation_b200 import api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_xcheck")
+N, SPRINT, TOTALTIME_MS, HOST_SEED = 65536, 2000, 6, 12345      # = GCFG_xcheck in oracle/Makefile
+
+
+def read_csv(path):
+    rows = [l.split(",") for l in open(path).read().splitlines() if l]
+    return [r[0] for r in rows], np.array([float(r[1]) for r in rows])
+
+
+@pytest.mark.gpu
+@pytest.mark.slow
+def test_t2_signal_agrees_with_reference_gpu_code(tmp_path):
+    if not os.path.exists(EXE):
+        pytest.skip("oracle/_ref/ref_gpu_xcheck not built (make -C oracle refgpu needs /root/reference)")
+    ref_csv, our_csv = str(tmp_path / "ref.csv"), str(tmp_path / "ours.csv")
+    out = subprocess.run([EXE, ref_csv], capture_output=True, text=True, timeout=900, cwd=str(tmp_path))
+    assert out.returncode == 0, out.stderr[-2000:]
+    m = re.search(r"Elapsed time: ([0-9.eE+]+) ms", out.stdout)
+    assert m, out.stdout[-2000:]
+    ref_ms = float(m.group(1))
+
+    p = api.ParameterStruct(num_water=N, sprintSteps=SPRINT, totaltime=TOTALTIME_MS)
+    assert p.t == 6_000_000 and p.tcp == 5_500_000 and p.pfreq == 1000
+    import time
+    t0 = time.perf_counter()
+    api.simulateWaters(our_csv, p, host_seed=HOST_SEED, walker_seed=0xC0FFEE, device=0)
+    our_s = time.perf_counter() - t0
+
+    t_ref, s_ref = read_csv(ref_csv)
+    t_our, s_our = read_csv(our_csv)
+    assert t_ref == t_our and len(t_ref) == p.t // p.pfreq                 # same rows, same time stamps, same formatting
+    assert s_ref[0] == pytest.approx(N, rel=1e-5) and s_our[0] == pytest.approx(N, rel=1e-5)
+    # Monte-Carlo error of the difference of two independent N-walker means of cos(phi):
+    # Var cos(phi) <= 1 - <cos phi>^2; 5 sigma, plus the CSV's 6 significant digits
+    mean = 0.5 * (s_ref + s_our) / N
+    tol = 5.0 * np.sqrt(2.0 * np.clip(1.0 - mean * mean, 0.0, 1.0) / N) + 2e-5
+    diff = np.abs(s_ref - s_our) / N
+    worst = int(np.argmax(diff - tol))
+    assert np.all(diff <= tol), (t_ref[worst], s_ref[worst], s_our[worst], diff[worst], tol[worst])
+    # the echo structure is there: the signal has decayed, and the CPMG flip at 5.5 ms bends it upward
+    assert s_our[-1] / N < 0.75 and s_ref[-1] / N < 0.75
+    k = p.tcp // p.pfreq
+    for s in (s_ref, s_our):
+        before = s[k - 1] - s[k - 101]           # slope over the 0.1 ms before the flip
+        after = s[k + 99] - s[k - 1]             # and after it
+        assert after > before
+    print(f"\nreference GPU code on this box: {N * p.t / (ref_ms * 1e-3):.3e} walker-steps/s ({ref_ms:.0f} ms); "
+          f"ours through simulateWaters (scene build + run + CSV): {N * p.t / our_s:.3e} walker-steps/s; "
+          f"max |dS|/N = {diff.max():.2e} (5-sigma bound at that row {tol[int(np.argmax(diff))]:.2e})")
