@@ -115,6 +115,28 @@ typedef struct mrisim_scene mrisim_scene;
 
 int  mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads,
                         mrisim_scene** out);
+/* Same scene, octree built on GPU `device` (replaces the 16 std::threads of
+ * Octree::Octree, octree.cpp:410-414, and build_subtree/grad/field, :215-333).  The result is
+ * byte-identical to mrisim_scene_build(): the leaf criterion and every float B sample are computed
+ * on the GPU with a rigorous error bound against the host's libm pow(); the few values whose bound
+ * straddles the decision threshold or a float rounding boundary are re-evaluated with libm on the
+ * host (counted in stats).  Fails (no CPU fallback) when the device is unusable. */
+typedef struct mrisim_octree_build_stats {
+    double   total_ms;          /* wall time of the octree build (GPU + fix-ups + linearisation)  */
+    double   gpu_ms;            /* of which: kernels, measured with CUDA events                   */
+    double   fixup_ms;          /* of which: host libm re-evaluations                             */
+    double   linearise_ms;      /* of which: depth-first linearisation on the host                */
+    uint64_t n_nodes, n_leaves, n_levels;
+    uint64_t criterion_evals, criterion_fixups;   /* leaf-criterion evaluations / re-done on host */
+    uint64_t b_values, b_fixups;                  /* float B samples / re-done on host            */
+    uint64_t pair_evals;        /* (point, dipole) terms evaluated on the GPU                     */
+    uint64_t kernel_launches;
+} mrisim_octree_build_stats;
+int  mrisim_scene_build_gpu(const mrisim_params* p, uint64_t host_seed, int n_threads, int device,
+                            mrisim_scene** out, mrisim_octree_build_stats* stats /* may be NULL */);
+/* test knob: multiplies the certified error bounds (default 1) so that the host fix-up path can be
+ * exercised at will; the result must not change. */
+void mrisim_octree_build_set_margin_scale(double scale);
 int  mrisim_scene_load(const char* path, mrisim_scene** out);     /* MRISCN01 file */
 int  mrisim_scene_save(const mrisim_scene* s, const char* path);
 void mrisim_scene_free(mrisim_scene* s);

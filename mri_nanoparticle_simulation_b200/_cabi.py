@@ -37,6 +37,18 @@ class Params(C.Structure):
         return q
 
 
+class OctreeBuildStats(C.Structure):
+    """``mrisim_octree_build_stats`` (include/mrisim.h)."""
+    _fields_ = [("total_ms", C.c_double), ("gpu_ms", C.c_double), ("fixup_ms", C.c_double), ("linearise_ms", C.c_double),
+                ("n_nodes", C.c_uint64), ("n_leaves", C.c_uint64), ("n_levels", C.c_uint64),
+                ("criterion_evals", C.c_uint64), ("criterion_fixups", C.c_uint64),
+                ("b_values", C.c_uint64), ("b_fixups", C.c_uint64), ("pair_evals", C.c_uint64),
+                ("kernel_launches", C.c_uint64)]
+
+    def asdict(self) -> dict:
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 #: ``mrisim_water`` == reference ``water_info`` (src/rand_walk.h:25-53), 40 bytes
 WATER_DTYPE = np.dtype({
     "names": ["x", "y", "z", "phase", "in_cell", "nearest"],

@@ -16,7 +16,7 @@ from typing import Optional
 import numpy as np
 
 from . import _cabi as cabi
-from ._cabi import FIELD_EXACT, FIELD_FAST, PATH_AUTO, PATH_FUSED, PATH_PIPELINE, KICK_CONSTANT, KICK_NONE, KICK_RANDOM, Params  # noqa: F401
+from ._cabi import FIELD_EXACT, FIELD_FAST, PATH_AUTO, PATH_FUSED, PATH_PIPELINE, KICK_CONSTANT, KICK_NONE, KICK_RANDOM, OctreeBuildStats, Params  # noqa: F401
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MRISIM_LIB") or os.path.join(PKG, "libmrisim.so")   # MRISIM_LIB: tuning builds only
@@ -45,6 +45,8 @@ def lib():
         "mrisim_params_derive": (None, [PP]),
         "mrisim_params_low_permeability": (None, [PP]),
         "mrisim_scene_build": (C.c_int, [PP, u64, C.c_int, C.POINTER(vp)]),
+        "mrisim_scene_build_gpu": (C.c_int, [PP, u64, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(OctreeBuildStats)]),
+        "mrisim_octree_build_set_margin_scale": (None, [C.c_double]),
         "mrisim_scene_load": (C.c_int, [C.c_char_p, C.POINTER(vp)]),
         "mrisim_scene_save": (C.c_int, [vp, C.c_char_p]),
         "mrisim_scene_free": (None, [vp]),
@@ -97,7 +99,7 @@ def lib():
 #: every symbol include/mrisim.h declares (tests check the library exports each one)
 ABI_SYMBOLS = [
     "mrisim_version", "mrisim_params_default", "mrisim_params_derive", "mrisim_params_low_permeability",
-    "mrisim_scene_build", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
+    "mrisim_scene_build", "mrisim_scene_build_gpu", "mrisim_octree_build_set_margin_scale", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters",
     "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
@@ -172,10 +174,19 @@ class BacteriaBox:
             raise MrisimError(lib().mrisim_scene_last_error().decode())
         return self
 
-    def populateSimulation(self) -> "BacteriaBox":
+    def populateSimulation(self, device: Optional[int] = None) -> "BacteriaBox":
+        """``device=None``: the octree is built by the host threads (as the reference does,
+        octree.cpp:410-414); ``device=k``: on GPU k (csrc/octree_build.cu), byte-identical result,
+        ``self.octree_build_stats`` then holds the builder's counters."""
         if self._h:
             return self
-        if lib().mrisim_scene_build(C.byref(self.params), self.seed, self.n_threads, C.byref(self._h)):
+        if device is None:
+            rc = lib().mrisim_scene_build(C.byref(self.params), self.seed, self.n_threads, C.byref(self._h))
+        else:
+            self.octree_build_stats = OctreeBuildStats()
+            rc = lib().mrisim_scene_build_gpu(C.byref(self.params), self.seed, self.n_threads, int(device),
+                                              C.byref(self._h), C.byref(self.octree_build_stats))
+        if rc:
             raise MrisimError(lib().mrisim_scene_last_error().decode())
         return self
 

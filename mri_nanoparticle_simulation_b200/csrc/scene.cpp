@@ -24,6 +24,7 @@
 
 #include "mrisim.h"
 #include "mrisim_math.h"
+#include "scene_internal.h"
 
 static_assert(sizeof(mrisim_params) == 192 && sizeof(mrisim_water) == 40 && sizeof(mrisim_mnp) == 40 &&
               sizeof(mrisim_node) == 48 && sizeof(mrisim_rng_state) == 24, "C ABI layouts (mirrored in _cabi.py)");
@@ -84,6 +85,30 @@ public:
 
     // octree.cpp:344-371 (one hashed subtree; `offset` is its index in the root table)
     void build_subtree_at(int offset, SubtreeOut& out) const {
+        double x, y, z, g; uint64_t mc;
+        root_of(offset, &x, &y, &z, &g, &mc);
+        std::vector<int> all(mnps_.size());
+        for (size_t i = 0; i < all.size(); i++) all[i] = (int)i;
+        std::vector<int> root_res = filter(all, x, y, z, g);
+        out.nodes.clear(); out.residents.clear();
+        descend(out, mc, root_res, x, y, z, g);
+    }
+
+    // seams for the GPU builder (scene_internal.h): the same expressions, one value at a time
+    double space_limit(double g) const { return std::pow(g / 2 * std::sqrt(3) + p_.scale * p_.cell_r, 2); }
+    double criterion(double x, double y, double z, double g) const {
+        return g / 2 * 1e-6 * grad(x + g / 2, y + g / 2, z + g / 2);
+    }
+    double leaf_B(const int32_t* res, size_t n_res, double xn, double yn, double zn) const {
+        double B = field(xn, yn, zn);
+        for (size_t k = 0; k < n_res; k++) {
+            const mrisim_mnp& m = mnps_[(size_t)res[k]];
+            double dx = xn - m.x, dy = yn - m.y, dz = zn - m.z;
+            B -= dipole(dx, dy, dz, m.M);
+        }
+        return B;
+    }
+    void root_of(int offset, double* xo, double* yo, double* zo, double* go, uint64_t* mco) const {
         double x = 0, y = 0, z = 0, g = p_.bound;
         int temp = offset;
         for (int j = min_depth - 1; j >= 0; j--) {
@@ -98,11 +123,7 @@ public:
         }
         uint64_t mc = host_morton(min_depth, x, y, z, p_.bound);
         mc |= (uint64_t)(int64_t)(1 << (3 * min_depth));       // int shift, octree.cpp:367
-        std::vector<int> all(mnps_.size());
-        for (size_t i = 0; i < all.size(); i++) all[i] = (int)i;
-        std::vector<int> root_res = filter(all, x, y, z, g);
-        out.nodes.clear(); out.residents.clear();
-        descend(out, mc, root_res, x, y, z, g);
+        *xo = x; *yo = y; *zo = z; *go = g; *mco = mc;
     }
 
 private:
@@ -113,7 +134,7 @@ private:
     // octree.cpp:168-174 MNP_in_space + :183-201 transfer_MNPs (index lists, same order)
     std::vector<int> filter(const std::vector<int>& src, double x, double y, double z, double g) const {
         std::vector<int> dst;
-        const double lim = std::pow(g / 2 * std::sqrt(3) + p_.scale * p_.cell_r, 2);
+        const double lim = space_limit(g);
         for (int i : src) {
             const mrisim_mnp& m = mnps_[i];
             double dx = x + g / 2 - m.x;
@@ -383,7 +404,7 @@ static void add_periodic_images(mrisim_scene& s) {
 
 // SimulationBox.cpp:86-88 + octree.cpp:388-450
 static void build_octree(mrisim_scene& s, int n_threads) {
-    OctreeBuilder ob(s.p, s.mnps, /*max_product=*/2e-6, /*max_g=*/5, /*min_g=*/.002);
+    OctreeBuilder ob(s.p, s.mnps, kMaxProduct, kMaxG, kMinG);
     s.min_depth = ob.min_depth; s.max_depth = ob.max_depth;
     const int n_sub = 1 << (3 * s.min_depth);
     std::vector<SubtreeOut> parts((size_t)n_sub);
@@ -404,6 +425,43 @@ static void build_octree(mrisim_scene& s, int n_threads) {
         s.residents.insert(s.residents.end(), parts[i].residents.begin(), parts[i].residents.end());
         parts[i] = SubtreeOut();
     }
+}
+
+// ---- seams for the GPU octree builder (scene_internal.h) -----------------------------
+void octree_depths(const mrisim_params& p, int32_t* min_depth, int32_t* max_depth) {
+    static const std::vector<mrisim_mnp> none;
+    OctreeBuilder ob(p, none, kMaxProduct, kMaxG, kMinG);
+    *min_depth = ob.min_depth; *max_depth = ob.max_depth;
+}
+void octree_root(const mrisim_params& p, int min_depth, int offset,
+                 double* x, double* y, double* z, double* g, uint64_t* mc) {
+    static const std::vector<mrisim_mnp> none;
+    OctreeBuilder ob(p, none, kMaxProduct, kMaxG, kMinG);
+    ob.min_depth = min_depth;
+    ob.root_of(offset, x, y, z, g, mc);
+}
+double octree_space_limit(const mrisim_params& p, double g) {
+    static const std::vector<mrisim_mnp> none;
+    return OctreeBuilder(p, none, kMaxProduct, kMaxG, kMinG).space_limit(g);
+}
+double octree_grad_limit(const mrisim_params& p) { return std::pow(p.scale * p.cell_r, 2); }
+double octree_criterion(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps,
+                        double x, double y, double z, double g) {
+    return OctreeBuilder(p, mnps, kMaxProduct, kMaxG, kMinG).criterion(x, y, z, g);
+}
+double octree_leaf_B(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps, const int32_t* res, size_t n_res,
+                     double xn, double yn, double zn) {
+    return OctreeBuilder(p, mnps, kMaxProduct, kMaxG, kMinG).leaf_B(res, n_res, xn, yn, zn);
+}
+
+// the GPU builder's output, moved into the scene (same canonical form as build_octree above)
+static void adopt_octree(mrisim_scene& s, OctreeOut& o) {
+    s.min_depth = o.min_depth; s.max_depth = o.max_depth;
+    s.subtree_sizes = std::move(o.subtree_sizes);
+    s.nodes = std::move(o.nodes);
+    s.residents = std::move(o.residents);
+    s.prefix.assign(s.subtree_sizes.size() + 1, 0);
+    for (size_t i = 0; i < s.subtree_sizes.size(); i++) s.prefix[i + 1] = s.prefix[i] + s.subtree_sizes[i];
 }
 
 // SimulationBox.cpp:131-147: std::sort (unstable) on the Morton code of the starting leaf,
@@ -490,7 +548,9 @@ void mrisim_params_low_permeability(mrisim_params* p) {
 
 const char* mrisim_scene_last_error(void) { return g_scene_error.c_str(); }
 
-int mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads, mrisim_scene** out) {
+// device < 0: octree on the host threads; device >= 0: octree_build.cu on that GPU
+static int scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads, int device,
+                       mrisim_scene** out, mrisim_octree_build_stats* stats) {
     if (!p || !out) { g_scene_error = "mrisim_scene_build: null argument"; return 1; }
     if (validate(*p)) return 1;
     std::unique_ptr<mrisim_scene> s(new mrisim_scene);
@@ -506,10 +566,30 @@ int mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads
         return 2;
     }
     add_periodic_images(*s);
-    build_octree(*s, n_threads);
+    if (device < 0) {
+        build_octree(*s, n_threads);
+    } else {
+        OctreeOut o;
+        std::string err;
+        if (build_octree_gpu(s->p, s->mnps, device, n_threads, o, stats, err)) {
+            g_scene_error = "mrisim_scene_build_gpu: " + err;
+            return 3;
+        }
+        adopt_octree(*s, o);
+    }
     sort_waters(*s, n_threads);
     *out = s.release();
     return 0;
+}
+
+int mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads, mrisim_scene** out) {
+    return scene_build(p, host_seed, n_threads, -1, out, nullptr);
+}
+
+int mrisim_scene_build_gpu(const mrisim_params* p, uint64_t host_seed, int n_threads, int device,
+                           mrisim_scene** out, mrisim_octree_build_stats* stats) {
+    if (device < 0) { g_scene_error = "mrisim_scene_build_gpu: device must be >= 0 (no CPU fallback on this entry point)"; return 1; }
+    return scene_build(p, host_seed, n_threads, device, out, stats);
 }
 
 int mrisim_scene_rethrow_waters(mrisim_scene* s, const mrisim_params* p, int64_t num_water, uint64_t seed, int sort_by_morton) {

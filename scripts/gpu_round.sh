@@ -7,7 +7,7 @@ tag=${1:-run}
 out=gpurun_out/$tag
 mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $out/gpu.txt 2>&1
-(time python -m pytest tests -m gpu -x -q) > $out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a $out/pytest_gpu.log
+(time python -m pytest tests -m gpu -x -q -rP) > $out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a $out/pytest_gpu.log
 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
 cat $out/bench.json
 python bench.py --field-mode fast --no-cpu-baseline --steps 3 > $out/bench_fast.json 2>> $out/bench.err
