@@ -222,6 +222,8 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--walkers-per-gpu", type=int, default=0, help="override the workload's walker count")
     ap.add_argument("--field-mode", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--path-mode", default="auto", choices=["auto", "fused", "pipeline"],
+                    help="fused: one thread per walker for the whole sprint; pipeline: the few-walker path; auto: by walker count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     args = ap.parse_args()
@@ -255,6 +257,7 @@ def main():
     n_int = steps // p.pfreq
     ctx = api.WalkerContext(p, local)
     ctx.set_field_mode(api.FIELD_FAST if args.field_mode == "fast" else api.FIELD_EXACT)
+    ctx.set_path_mode({"auto": api.PATH_AUTO, "fused": api.PATH_FUSED, "pipeline": api.PATH_PIPELINE}[args.path_mode])
     ctx.set_scene(box)
     ctx.set_waters(waters, WALKER_SEED, rank * n_per_gpu)
 
@@ -361,6 +364,7 @@ def main():
         "config": {"workload": args.workload, "walkers_per_gpu": n_per_gpu, "walkers_total": n_total,
                    "sprintSteps": steps, "signal_samples_per_step": n_int, "num_cells": p.num_cells,
                    "octree_nodes": int(len(box.getOctree().nodes)), "field_mode": args.field_mode,
+                   "path_mode": args.path_mode, "pipeline_sprints": ctx.pipeline_sprints,
                    "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
                    "parallelism": f"walker-sharded x{world}, scene replicated, 1 all-reduce of {n_int} f64 per step"},
         "e2e": {"value": e2e_value, "unit": "walker-steps/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -131,6 +131,9 @@ typedef struct mrisim_octree_build_stats {
     uint64_t b_values, b_fixups;                  /* float B samples / re-done on host            */
     uint64_t pair_evals;        /* (point, dipole) terms evaluated on the GPU                     */
     uint64_t kernel_launches;
+    /* the other stages of mrisim_scene_build_gpu (csrc/scene_gpu.cu), wall ms:
+     * water throw (candidates + containment + compaction), lookup table, Morton keys + std::sort */
+    double   scene_throw_ms, scene_lookup_ms, scene_sort_ms;
 } mrisim_octree_build_stats;
 int  mrisim_scene_build_gpu(const mrisim_params* p, uint64_t host_seed, int n_threads, int device,
                             mrisim_scene** out, mrisim_octree_build_stats* stats /* may be NULL */);
@@ -158,6 +161,11 @@ int  mrisim_scene_octree(const mrisim_scene* s, int32_t* min_depth, int32_t* max
  * octree.  BacteriaBox::init_waters + SimulationBox::sortWaters semantics otherwise. */
 int  mrisim_scene_rethrow_waters(mrisim_scene* s, const mrisim_params* p, int64_t num_water,
                                  uint64_t seed, int sort_by_morton);
+/* same waters, thrown on GPU `device`: attempts generated from recorded states of the host stream,
+ * containment tested against every cell (SimulationBox.cpp:161-173), accepted in stream order,
+ * leaf Morton keys from a GPU descent; only the std::sort stays on the host.  Bit-identical. */
+int  mrisim_scene_rethrow_waters_gpu(mrisim_scene* s, const mrisim_params* p, int64_t num_water,
+                                     uint64_t seed, int sort_by_morton, int device);
 
 /* -------------------------------------------------------------------------------------
  * Device context: replaces the body of simulateWaters() between populateSimulation() and

@@ -58,6 +58,7 @@ def lib():
         "mrisim_scene_octree": (C.c_int, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp), C.POINTER(i32),
                                           C.POINTER(vp), C.POINTER(u64), C.POINTER(vp), C.POINTER(u64)]),
         "mrisim_scene_rethrow_waters": (C.c_int, [vp, PP, i64, u64, C.c_int]),
+        "mrisim_scene_rethrow_waters_gpu": (C.c_int, [vp, PP, i64, u64, C.c_int, C.c_int]),
         "mrisim_create": (C.c_int, [PP, C.c_int, C.POINTER(vp)]),
         "mrisim_destroy": (None, [vp]),
         "mrisim_last_error": (C.c_char_p, [vp]),
@@ -101,7 +102,7 @@ ABI_SYMBOLS = [
     "mrisim_version", "mrisim_params_default", "mrisim_params_derive", "mrisim_params_low_permeability",
     "mrisim_scene_build", "mrisim_scene_build_gpu", "mrisim_octree_build_set_margin_scale", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
-    "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters",
+    "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters", "mrisim_scene_rethrow_waters_gpu",
     "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
@@ -194,9 +195,14 @@ class BacteriaBox:
         if lib().mrisim_scene_save(self._handle(), path.encode()):
             raise MrisimError(lib().mrisim_scene_last_error().decode())
 
-    def rethrow_waters(self, num_water: int, seed: int, sort_by_morton: bool = True, params: Optional[Params] = None):
-        if lib().mrisim_scene_rethrow_waters(self._handle(), C.byref(params) if params is not None else None,
-                                              num_water, seed, int(sort_by_morton)):
+    def rethrow_waters(self, num_water: int, seed: int, sort_by_morton: bool = True, params: Optional[Params] = None,
+                       device: Optional[int] = None):
+        pp = C.byref(params) if params is not None else None
+        if device is None:
+            rc = lib().mrisim_scene_rethrow_waters(self._handle(), pp, num_water, seed, int(sort_by_morton))
+        else:
+            rc = lib().mrisim_scene_rethrow_waters_gpu(self._handle(), pp, num_water, seed, int(sort_by_morton), int(device))
+        if rc:
             raise MrisimError(lib().mrisim_scene_last_error().decode())
 
     def _handle(self):

@@ -29,7 +29,7 @@ NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-line
              [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK", "MRISIM_TERMS_PER_TRIP") if os.environ.get(k)]
 CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC]
 
-CU_SOURCES = ["mrisim.cu", "octree_build.cu"]
+CU_SOURCES = ["mrisim.cu", "octree_build.cu", "scene_gpu.cu"]
 CXX_SOURCES = ["scene.cpp", "simulate_waters.cpp"]
 
 

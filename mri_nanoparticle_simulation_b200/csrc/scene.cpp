@@ -14,6 +14,7 @@
 // glibc): the leaf criterion and the float B samples go through libm pow().
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -249,6 +250,10 @@ uint64_t scene_find_leaf(const mrisim_scene& s, double wx, double wy, double wz)
     return n;
 }
 
+static double wall_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 static int hw_threads(int n_threads) {
     if (n_threads > 0) return n_threads;
     unsigned h = std::thread::hardware_concurrency();
@@ -467,21 +472,32 @@ static void adopt_octree(mrisim_scene& s, OctreeOut& o) {
 // SimulationBox.cpp:131-147: std::sort (unstable) on the Morton code of the starting leaf,
 // leaf bit included.  The permutation produced by libstdc++'s introsort depends only on
 // the comparison results, so sorting (key, index) pairs reproduces the reference's order.
-static void sort_waters(mrisim_scene& s, int n_threads) {
+static int sort_waters(mrisim_scene& s, int n_threads, int device = -1) {
     struct Key { uint64_t mc; uint32_t idx; };
     const int64_t n = (int64_t)s.waters.size();
     std::vector<Key> keys((size_t)n);
-    const int64_t chunk = 1024, n_chunks = (n + chunk - 1) / chunk;
-    parallel_for(n_chunks, n_threads, [&](int64_t c) {
-        for (int64_t i = c * chunk; i < std::min(n, (c + 1) * chunk); i++) {
-            const mrisim_water& w = s.waters[(size_t)i];
-            keys[(size_t)i] = Key{s.nodes[scene_find_leaf(s, w.x, w.y, w.z)].mc, (uint32_t)i};
+    if (device < 0) {
+        const int64_t chunk = 1024, n_chunks = (n + chunk - 1) / chunk;
+        parallel_for(n_chunks, n_threads, [&](int64_t c) {
+            for (int64_t i = c * chunk; i < std::min(n, (c + 1) * chunk); i++) {
+                const mrisim_water& w = s.waters[(size_t)i];
+                keys[(size_t)i] = Key{s.nodes[scene_find_leaf(s, w.x, w.y, w.z)].mc, (uint32_t)i};
+            }
+        });
+    } else {                       // leaf codes from the GPU descent (scene_gpu.cu), same values
+        std::vector<uint64_t> mc;
+        std::string err;
+        if (gpu_leaf_keys(s.p, s.min_depth, s.prefix, s.nodes, s.waters, device, mc, err)) {
+            g_scene_error = "gpu_leaf_keys: " + err;
+            return 1;
         }
-    });
+        for (int64_t i = 0; i < n; i++) keys[(size_t)i] = Key{mc[(size_t)i], (uint32_t)i};
+    }
     std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) { return a.mc < b.mc; });
     std::vector<mrisim_water> sorted((size_t)n);
     for (int64_t i = 0; i < n; i++) sorted[(size_t)i] = s.waters[keys[(size_t)i].idx];
     s.waters.swap(sorted);
+    return 0;
 }
 
 static int validate(const mrisim_params& p) {
@@ -559,25 +575,44 @@ static int scene_build(const mrisim_params* p, uint64_t host_seed, int n_threads
     // SimulationBox.cpp:77-97, in the reference's order (it fixes the RNG consumption order)
     throw_cells(*s, gen);
     place_dipoles(*s);
-    throw_waters(*s, gen, p->num_water, n_threads);
-    if (build_lookup(*s, n_threads)) {
+    std::string err;
+    const double t0 = wall_ms();
+    if (device < 0) {
+        throw_waters(*s, gen, p->num_water, n_threads);
+    } else if (gpu_throw_waters(s->p, s->cells, &gen.r, p->num_water, device, s->waters, err)) {
+        g_scene_error = "mrisim_scene_build_gpu: " + err;
+        return 3;
+    }
+    const double t1 = wall_ms();
+    int overflow = 0;
+    if (device < 0) {
+        overflow = build_lookup(*s, n_threads);
+    } else if (gpu_build_lookup(s->p, s->cells, device, s->lookup, &overflow, err)) {
+        g_scene_error = "mrisim_scene_build_gpu: " + err;
+        return 3;
+    }
+    if (overflow) {
         g_scene_error = "mrisim_scene_build: a lookup-table row holds >= maxNeighbors cells "
                         "(the reference asserts here, SimulationBox.cpp:281); raise maxNeighbors or hashDim";
         return 2;
     }
+    const double t2 = wall_ms();
     add_periodic_images(*s);
     if (device < 0) {
         build_octree(*s, n_threads);
     } else {
         OctreeOut o;
-        std::string err;
         if (build_octree_gpu(s->p, s->mnps, device, n_threads, o, stats, err)) {
             g_scene_error = "mrisim_scene_build_gpu: " + err;
             return 3;
         }
         adopt_octree(*s, o);
     }
-    sort_waters(*s, n_threads);
+    const double t3 = wall_ms();
+    if (sort_waters(*s, n_threads, device)) return 3;
+    if (stats && device >= 0) {
+        stats->scene_throw_ms = t1 - t0; stats->scene_lookup_ms = t2 - t1; stats->scene_sort_ms = wall_ms() - t3;
+    }
     *out = s.release();
     return 0;
 }
@@ -592,14 +627,32 @@ int mrisim_scene_build_gpu(const mrisim_params* p, uint64_t host_seed, int n_thr
     return scene_build(p, host_seed, n_threads, device, out, stats);
 }
 
-int mrisim_scene_rethrow_waters(mrisim_scene* s, const mrisim_params* p, int64_t num_water, uint64_t seed, int sort_by_morton) {
+static int rethrow(mrisim_scene* s, const mrisim_params* p, int64_t num_water, uint64_t seed, int sort_by_morton, int device) {
     if (!s || num_water < 0) { g_scene_error = "mrisim_scene_rethrow_waters: bad argument"; return 1; }
     if (p) { s->p.avoid_intracellular_throw = p->avoid_intracellular_throw; s->p.water_start_bound = p->water_start_bound; }
     HostRng gen(seed);
-    throw_waters(*s, gen, num_water, 0);
-    if (sort_by_morton) sort_waters(*s, 0);
+    if (device < 0) {
+        throw_waters(*s, gen, num_water, 0);
+    } else {
+        std::string err;
+        if (gpu_throw_waters(s->p, s->cells, &gen.r, num_water, device, s->waters, err)) {
+            g_scene_error = "mrisim_scene_rethrow_waters_gpu: " + err;
+            return 3;
+        }
+    }
+    if (sort_by_morton && sort_waters(*s, 0, device)) return 3;
     s->p.num_water = (int32_t)std::min<int64_t>(num_water, INT32_MAX);
     return 0;
+}
+
+int mrisim_scene_rethrow_waters(mrisim_scene* s, const mrisim_params* p, int64_t num_water, uint64_t seed, int sort_by_morton) {
+    return rethrow(s, p, num_water, seed, sort_by_morton, -1);
+}
+
+int mrisim_scene_rethrow_waters_gpu(mrisim_scene* s, const mrisim_params* p, int64_t num_water, uint64_t seed,
+                                    int sort_by_morton, int device) {
+    if (device < 0) { g_scene_error = "mrisim_scene_rethrow_waters_gpu: device must be >= 0 (no CPU fallback on this entry point)"; return 1; }
+    return rethrow(s, p, num_water, seed, sort_by_morton, device);
 }
 
 void mrisim_scene_free(mrisim_scene* s) { delete s; }

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "mrisim.h"
+#include "mrisim_math.h"
 
 namespace mrisim_host {
 
@@ -37,5 +38,14 @@ double octree_leaf_B(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
 // ---- GPU builder (octree_build.cu)
 int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps, int device, int n_threads,
                      OctreeOut& out, mrisim_octree_build_stats* stats, std::string& err);
+
+// ---- the other O(N x cells) loops of the scene build on the GPU (scene_gpu.cu)
+int gpu_build_lookup(const mrisim_params& p, const std::vector<double>& cells, int device,
+                     std::vector<int32_t>& lookup, int* overflow, std::string& err);
+int gpu_throw_waters(const mrisim_params& p, const std::vector<double>& cells, mrisim_rng* gen, int64_t num_water,
+                     int device, std::vector<mrisim_water>& waters, std::string& err);
+int gpu_leaf_keys(const mrisim_params& p, int min_depth, const std::vector<uint64_t>& prefix,
+                  const std::vector<mrisim_node>& nodes, const std::vector<mrisim_water>& waters, int device,
+                  std::vector<uint64_t>& keys, std::string& err);
 
 }  // namespace mrisim_host

@@ -35,8 +35,31 @@ def build(cfg, seed, device):
     return dt, digest, len(oc.nodes), len(oc.residents), getattr(box, "octree_build_stats", None)
 
 
+def waters_bench(n):
+    """mrisim_scene_rethrow_waters (host threads) vs _gpu on the dense2000 scene, n waters."""
+    cfg, seed = SCENES["dense2000"]
+    p = api.ParameterStruct(**cfg)
+    box = api.BacteriaBox(p, seed).populateSimulation(device=0)
+    box.rethrow_waters(4096, 5, device=0)                      # warm-up
+    row = {"waters": n, "scene": "dense2000"}
+    digests = []
+    for name, dev in (("gpu", 0), ("host", None)):
+        for sort in (False, True):
+            t0 = time.perf_counter()
+            box.rethrow_waters(n, 5, sort_by_morton=sort, device=dev)
+            row[f"{name}_{'sorted' if sort else 'throw_only'}_s"] = round(time.perf_counter() - t0, 4)
+        digests.append(hashlib.sha256(box.getWaters().tobytes()).hexdigest())
+    row["byte_identical"] = digests[0] == digests[1]
+    row["host_threads"] = os.cpu_count()
+    print(json.dumps(row), flush=True)
+
+
 def main():
     args = sys.argv[1:]
+    if args and args[0] == "--waters":
+        for n in args[1:]:
+            waters_bench(int(n))
+        return
     no_host = set()
     if "--no-host" in args:
         k = args.index("--no-host")
