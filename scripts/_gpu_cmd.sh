@@ -1,15 +1,20 @@
-mkdir -p gpurun_out/oct4
-(timeout 900 python -m pytest tests/test_octree_gpu.py -m "gpu" -x -q 2>&1 | tail -15) > gpurun_out/oct4/pytest.log; tail -4 gpurun_out/oct4/pytest.log
-timeout 600 python scripts/sweep_config5.py --waters 1048576 --sprints 1 --mmoments 3.5e-17,7e-17 --stdev-factors 1,2 > gpurun_out/oct4/sweep_1gpu_small.jsonl 2> gpurun_out/oct4/sweep.err; cat gpurun_out/oct4/sweep_1gpu_small.jsonl; tail -3 gpurun_out/oct4/sweep.err
-for wl in cfg1_default_4032_waters cfg2_8000_waters_intracellular_kick cfg3_lowperm_100k_waters; do for pm in auto fused; do
-  timeout 600 python bench.py --workload $wl --path-mode $pm --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/oct4/bench_${wl}_${pm}.json 2>> gpurun_out/oct4/bench.err
-  python -c "import json,sys; d=json.load(open('gpurun_out/oct4/bench_${wl}_${pm}.json')); print('$wl','$pm',d['value'],d['e2e']['value'],d['ms_per_step'],d['config'].get('pipeline_sprints'),d['gpu_launches'])"
+mkdir -p gpurun_out/pipe4
+(timeout 900 python -m pytest tests/test_gpu_parity.py -m "gpu and not slow" -x -q -k "pipeline or smoke or dropin" 2>&1 | tail -15) > gpurun_out/pipe4/pytest.log; tail -4 gpurun_out/pipe4/pytest.log
+for wl in cfg1_default_4032_waters cfg2_8000_waters_intracellular_kick cfg3_lowperm_100k_waters; do for pm in auto pipeline; do
+  timeout 600 python bench.py --workload $wl --path-mode $pm --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/pipe4/bench_${wl}_${pm}.json 2>> gpurun_out/pipe4/bench.err
+  python -c "import json,sys; d=json.load(open('gpurun_out/pipe4/bench_${wl}_${pm}.json')); print('$wl','$pm',d['value'],d['e2e']['value'],d['ms_per_step'],d['config'].get('pipeline_sprints'),d['gpu_launches'])"
 done; done
-tail -3 gpurun_out/oct4/bench.err
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:leaf_field_kernel -s 8 -c 1 -o /tmp/leaf_prof python scripts/octree_bench.py --no-host dense2000 > gpurun_out/oct4/ncu_leaf.log 2>&1; tail -2 gpurun_out/oct4/ncu_leaf.log
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:criterion_kernel -s 8 -c 1 -o /tmp/crit_prof python scripts/octree_bench.py --no-host dense2000 > gpurun_out/oct4/ncu_crit.log 2>&1; tail -2 gpurun_out/oct4/ncu_crit.log
-ncu -i /tmp/leaf_prof.ncu-rep --page raw --csv > gpurun_out/oct4/leaf_field_raw.csv 2>/dev/null
-ncu -i /tmp/crit_prof.ncu-rep --page raw --csv > gpurun_out/oct4/criterion_raw.csv 2>/dev/null
-ncu -i /tmp/leaf_prof.ncu-rep --page details > gpurun_out/oct4/leaf_field_details.txt 2>/dev/null
-ncu -i /tmp/crit_prof.ncu-rep --page details > gpurun_out/oct4/criterion_details.txt 2>/dev/null
-ls -la gpurun_out/oct4
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/pipe4/launches_cfg1_auto.csv python bench.py --workload cfg1_default_4032_waters --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/pipe4/ncu_cfg1.log 2>&1
+python - <<'PY'
+import csv, collections
+rows=list(csv.reader(open('gpurun_out/pipe4/launches_cfg1_auto.csv')))
+for i,r in enumerate(rows):
+    if r and r[0]=='ID': h=i;break
+hdr=rows[h]; ix={k:j for j,k in enumerate(hdr)}
+agg=collections.OrderedDict()
+for r in rows[h+1:]:
+    if len(r)<len(hdr): continue
+    name=r[ix['Kernel Name']].split('(')[0].split('::')[-1][:40]
+    a=agg.setdefault(name,[0,0.0]); a[0]+=1; a[1]+=float(r[ix['Metric Value']])
+for k,v in agg.items(): print(f"{k:42s} n={v[0]:4d} total={v[1]/1e6:9.3f} ms")
+PY
