@@ -184,9 +184,10 @@ enum {
  *   FUSED    one thread per walker, the whole step in registers (many walkers: issue-bound).
  *   PIPELINE the reference's own split (cuda_sim.cu:976-1013: draws, diffusion, phase accumulation,
  *            block sum), for FEW walkers where one thread per walker leaves the GPU latency-bound:
- *            draws per (walker, chunk) from GF(2) jump-ahead states, a serial position kernel, the
- *            field per (walker, step), ordered block sums.  Needs even pfreq and whole intervals.
- *   AUTO     PIPELINE up to 49 152 walkers, FUSED above (default). */
+ *            draws per (walker, draw-chunk) from GF(2) jump-ahead states, the position recursion
+ *            with one WARP per walker (32 speculative steps per trip, membrane tests side by side),
+ *            the field per (walker, step), ordered block sums.  Needs even pfreq and whole intervals.
+ *   AUTO     PIPELINE up to 36 864 walkers, FUSED above (default). */
 enum {
     MRISIM_PATH_AUTO = 0,
     MRISIM_PATH_FUSED = 1,
