@@ -51,6 +51,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to
+# fd 1 from C whatever NCCL_DEBUG_FILE says on some boxes), so fd 1 is pointed at stderr for the whole
+# run and the result line goes to a private duplicate of the original stdout.
+_RESULT_OUT = None
+
+
+def claim_stdout():
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _RESULT_OUT if _RESULT_OUT is not None else sys.stdout
+    print(json.dumps(line), file=out, flush=True)
+
+
 # ----------------------------------------------------------------------------------------
 def make_params(api, name):
     over, seed, n = WORKLOADS[name]
@@ -208,7 +227,7 @@ def run_reference_arm(args, api, ol):
         "e2e": {"value": value, "unit": "walker-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -227,6 +246,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     args = ap.parse_args()
+    claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: W < 3 warm-up steps does not meet the timing rules")
 
@@ -389,7 +409,7 @@ def main():
         line["cpu_baseline"] = {"value": n * steps / dt, "unit": "walker-steps/s", "cores": n_threads, "kind": "port",
                                 "sample": f"first {n} walkers of rank 0 x {steps} timesteps (one sprint), {dt:.1f} s, "
                                           f"{n_threads} pthreads over walkers"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

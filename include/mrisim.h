@@ -124,7 +124,7 @@ int  mrisim_scene_build(const mrisim_params* p, uint64_t host_seed, int n_thread
 typedef struct mrisim_octree_build_stats {
     double   total_ms;          /* wall time of the octree build (GPU + fix-ups + linearisation)  */
     double   gpu_ms;            /* of which: kernels, measured with CUDA events                   */
-    double   fixup_ms;          /* of which: host libm re-evaluations                             */
+    double   fixup_ms;          /* host libm re-evaluations (thread time; they run beside the GPU work)  */
     double   linearise_ms;      /* of which: depth-first linearisation on the host                */
     uint64_t n_nodes, n_leaves, n_levels;
     uint64_t criterion_evals, criterion_fixups;   /* leaf-criterion evaluations / re-done on host */
@@ -134,6 +134,7 @@ typedef struct mrisim_octree_build_stats {
     /* the other stages of mrisim_scene_build_gpu (csrc/scene_gpu.cu), wall ms:
      * water throw (candidates + containment + compaction), lookup table, Morton keys + std::sort */
     double   scene_throw_ms, scene_lookup_ms, scene_sort_ms;
+    double   fixup_wait_ms;     /* part of fixup_ms the build had to wait for after its last kernel      */
 } mrisim_octree_build_stats;
 int  mrisim_scene_build_gpu(const mrisim_params* p, uint64_t host_seed, int n_threads, int device,
                             mrisim_scene** out, mrisim_octree_build_stats* stats /* may be NULL */);

@@ -44,7 +44,8 @@ class OctreeBuildStats(C.Structure):
                 ("criterion_evals", C.c_uint64), ("criterion_fixups", C.c_uint64),
                 ("b_values", C.c_uint64), ("b_fixups", C.c_uint64), ("pair_evals", C.c_uint64),
                 ("kernel_launches", C.c_uint64),
-                ("scene_throw_ms", C.c_double), ("scene_lookup_ms", C.c_double), ("scene_sort_ms", C.c_double)]
+                ("scene_throw_ms", C.c_double), ("scene_lookup_ms", C.c_double), ("scene_sort_ms", C.c_double),
+                ("fixup_wait_ms", C.c_double)]
 
     def asdict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -327,6 +327,9 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
 
     // level min_depth: the subtree roots (octree.cpp:346-367), corners and codes from the host expressions
     std::vector<HostLevel> levels;
+    levels.reserve(64);                      // the fix-up threads keep pointers into it (depth <= 21 by the Morton width)
+    struct Fixers { std::vector<std::thread> th; void join() { for (auto& t : th) if (t.joinable()) t.join(); th.clear(); } ~Fixers() { join(); } } fixers;
+    std::atomic<double> fix_ms{0.0};
     DevLevel cur;
     double g = 0;
     {
@@ -480,18 +483,24 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         OB_CK(cudaStreamSynchronize(st));
         OB_CK(cudaGetLastError());
         { float ms = 0; OB_CK(cudaEventElapsedTime(&ms, ev0, ev1)); st_.gpu_ms += ms; }
-        if (n_unc_b) {     // samples whose bound straddles a float rounding boundary: the host's libm decides
-            const double t0 = now_ms();
-            parallel_for(n_unc_b, n_threads, [&](size_t k) {
-                const uint32_t i = unc_b[k] >> 3, o = unc_b[k] & 7;
-                const double xn = H.x[i] + g / 4 + (double)((o >> 2) & 1) * g / 2;
-                const double yn = H.y[i] + g / 2 + (double)((o >> 1) & 1) * g / 2;
-                const double zn = H.z[i] + g / 2 + (double)((o >> 0) & 1) * g / 2;
-                const float Bf = (float)octree_leaf_B(p, mnps, H.pool.data() + H.off[i], H.cnt[i], xn, yn, zn);
-                std::memcpy(&H.Bbits[(size_t)i * 8 + o], &Bf, 4);
-            });
+        if (n_unc_b) {     // samples whose bound straddles a float rounding boundary: the host's libm decides,
+                           // on its own threads, while the GPU goes on with the next level
+            HostLevel* Hp = &H;
+            const double gl = g;
             st_.b_fixups += n_unc_b;
-            st_.fixup_ms += now_ms() - t0;
+            fixers.th.emplace_back([&p, &mnps, Hp, gl, n_threads, &fix_ms, unc = std::move(unc_b)]() {
+                const double t0 = now_ms();
+                parallel_for(unc.size(), n_threads, [&](size_t k) {
+                    const uint32_t i = unc[k] >> 3, o = unc[k] & 7;
+                    const double xn = Hp->x[i] + gl / 4 + (double)((o >> 2) & 1) * gl / 2;
+                    const double yn = Hp->y[i] + gl / 2 + (double)((o >> 1) & 1) * gl / 2;
+                    const double zn = Hp->z[i] + gl / 2 + (double)((o >> 0) & 1) * gl / 2;
+                    const float Bf = (float)octree_leaf_B(p, mnps, Hp->pool.data() + Hp->off[i], Hp->cnt[i], xn, yn, zn);
+                    std::memcpy(&Hp->Bbits[(size_t)i * 8 + o], &Bf, 4);
+                });
+                double cur_ms = fix_ms.load();
+                while (!fix_ms.compare_exchange_weak(cur_ms, cur_ms + (now_ms() - t0))) {}
+            });
         }
         st_.n_leaves += n_leaf; st_.n_nodes += n; st_.n_levels++;
         if (!n_child) break;
@@ -499,6 +508,12 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         g = gc;
     }
 
+    {   // the libm re-evaluations still running: wait (only this part of them is on the critical path)
+        const double t0 = now_ms();
+        fixers.join();
+        st_.fixup_wait_ms = now_ms() - t0;
+        st_.fixup_ms = fix_ms.load();
+    }
     // ---- depth-first linearisation (octree.cpp:303-322 order), subtree by subtree
     const double t_lin = now_ms();
     out.subtree_sizes.assign(n_roots, 0);

@@ -1,25 +1,4 @@
-mkdir -p gpurun_out/pipe6
-(timeout 900 python -m pytest tests/test_gpu_parity.py -m "gpu and not slow" -x -q -k "pipeline or path_mode or full_default or cfg3 or dropin" 2>&1 | tail -15) > gpurun_out/pipe6/pytest.log; tail -4 gpurun_out/pipe6/pytest.log
-for wl in cfg1_default_4032_waters cfg2_8000_waters_intracellular_kick; do for pm in auto; do
-  timeout 600 python bench.py --workload $wl --path-mode $pm --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/pipe6/bench_${wl}_${pm}.json 2>> gpurun_out/pipe6/bench.err
-  python -c "import json,sys; d=json.load(open('gpurun_out/pipe6/bench_${wl}_${pm}.json')); print('$wl','$pm',d['value'],d['e2e']['value'],d['ms_per_step'],d['config'].get('pipeline_sprints'),d['gpu_launches'])"
-done; done
-for n in 16384 32768 49152 65536; do
-  for pm in fused pipeline; do
-  timeout 600 python bench.py --workload cfg1_default_4032_waters --walkers-per-gpu $n --path-mode $pm --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/pipe6/bench_n${n}_${pm}.json 2>> gpurun_out/pipe6/bench.err
-  python -c "import json,sys; d=json.load(open('gpurun_out/pipe6/bench_n${n}_${pm}.json')); print('n=$n','$pm',d['value'],d['ms_per_step'])"
-done; done
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/pipe6/launches_cfg1_auto.csv python bench.py --workload cfg1_default_4032_waters --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/pipe6/ncu_cfg1.log 2>&1
-python - <<'PY'
-import csv, collections
-rows=list(csv.reader(open('gpurun_out/pipe6/launches_cfg1_auto.csv')))
-for i,r in enumerate(rows):
-    if r and r[0]=='ID': h=i;break
-hdr=rows[h]; ix={k:j for j,k in enumerate(hdr)}
-agg=collections.OrderedDict()
-for r in rows[h+1:]:
-    if len(r)<len(hdr): continue
-    name=r[ix['Kernel Name']].split('(')[0].split('::')[-1][:40]
-    a=agg.setdefault(name,[0,0.0]); a[0]+=1; a[1]+=float(r[ix['Metric Value']])
-for k,v in agg.items(): print(f"{k:42s} n={v[0]:4d} total={v[1]/1e6:9.3f} ms")
-PY
+mkdir -p gpurun_out/v12
+(timeout 900 python -m pytest tests/test_octree_gpu.py -m gpu -x -q 2>&1 | tail -6) > gpurun_out/v12/pytest_octree.log; tail -3 gpurun_out/v12/pytest_octree.log
+timeout 900 python scripts/octree_bench.py default dense2000 --no-host dense8000 > gpurun_out/v12/octree_bench.jsonl 2> gpurun_out/v12/octree_bench.err; cut -c1-900 gpurun_out/v12/octree_bench.jsonl; tail -3 gpurun_out/v12/octree_bench.err
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/v12/bench_2gpu.json 2> gpurun_out/v12/bench2.err; echo "bench2 exit $?"; wc -l gpurun_out/v12/bench_2gpu.json; head -c 150 gpurun_out/v12/bench_2gpu.json
