@@ -169,6 +169,107 @@ leaf_field_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __re
     if (!certain) unc_list[atomicAdd(unc_count, 1u)] = i * 8 + o;
 }
 
+// ---- warp-cooperative variants for SMALL levels --------------------------------------------------
+// Near the root a level has a few hundred nodes: one thread per node then walks all dipoles alone,
+// ~0.46 us per dipole, 2.5 ms per level whatever the grid size (ncu: 13 % of the warp slots busy).
+// Here a WARP owns the node / sample point: the 32 lanes evaluate 32 dipoles' terms side by side,
+// and the running sums take them IN TABLE ORDER through shuffles -- the order is part of the result
+// (it is the host's `ret += ...`), so the values are those of the kernels above bit for bit.  The
+// sum|term| bound is order-free and is reduced at the end.  ~5x the issue slots per pair of the
+// thread-per-point kernels, so only used while a level is latency-bound (kWarpNodes / kWarpPoints).
+constexpr uint32_t kWarpNodes = 20000, kWarpPoints = 24000;
+constexpr unsigned kFullMask = 0xffffffffu;
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads)
+criterion_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
+                      const double* __restrict__ z, uint32_t n, double g, double grad_lim, double max_prod, double margin_scale,
+                      uint8_t* __restrict__ leaf, uint32_t* __restrict__ unc_list, uint32_t* __restrict__ unc_count) {
+    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const double px = x[i] + g / 2, py = y[i] + g / 2, pz = z[i] + g / 2;
+    double rx = 0, ry = 0, rz = 0, ax = 0, ay = 0, az = 0, sx = 0, sy = 0, sz = 0;
+    for (int k0 = 0; k0 < n_mnp; k0 += 32) {
+        const int cnt = min(32, n_mnp - k0);
+        double tx = 0.0, ty = 0.0, tz = 0.0;
+        if ((int)lane < cnt) {
+            const double4 m = mnp[k0 + lane];
+            const double dx = px - m.x, dy = py - m.y, dz = pz - m.z, M = m.w;
+            const double r2 = normsq(dx, dy, dz);
+            const bool on = r2 > grad_lim;
+            const double divisor = r2 * r2 * r2 * sqrt(r2);
+            const double xy = dx * dx + dy * dy;
+            const double a = 1 * xy - 4 * dz * dz;
+            const double c = 3 * xy - 2 * dz * dz;
+            tx = 3e17 * M * dx * a / divisor;
+            ty = 3e17 * M * dy * a / divisor;
+            tz = 3e17 * M * dz * c / divisor;
+            tx = on ? tx : 0.0; ty = on ? ty : 0.0; tz = on ? tz : 0.0;
+            ax += fabs(tx); ay += fabs(ty); az += fabs(tz);
+        }
+        for (int j = 0; j < cnt; j++) {
+            rx += __shfl_sync(kFullMask, tx, j); ry += __shfl_sync(kFullMask, ty, j); rz += __shfl_sync(kFullMask, tz, j);
+            sx += fabs(rx); sy += fabs(ry); sz += fabs(rz);
+        }
+    }
+    ax = warp_sum_d(ax) * 1.000001; ay = warp_sum_d(ay) * 1.000001; az = warp_sum_d(az) * 1.000001;
+    if (lane) return;
+    const double grad = sqrt(normsq(rx, ry, rz));
+    const double lhs = g / 2 * 1e-6 * grad;
+    const double ex = kRelTerm * ax + kRelSum * sx, ey = kRelTerm * ay + kRelSum * sy, ez = kRelTerm * az + kRelSum * sz;
+    const double eg = sqrt(normsq(ex, ey, ez)) + 0x1p-49 * grad;
+    const double e = (g / 2 * 1e-6) * eg * margin_scale * 1.000001;
+    const bool is_leaf = lhs < max_prod;
+    const bool certain = isfinite(lhs) && isfinite(e) && ((lhs - e < max_prod) == (lhs + e < max_prod));
+    leaf[i] = is_leaf ? 1 : 0;
+    if (!certain) unc_list[atomicAdd(unc_count, 1u)] = i;
+}
+
+__global__ void __launch_bounds__(kThreads)
+leaf_field_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
+                       const double* __restrict__ z, const uint32_t* __restrict__ off, const uint32_t* __restrict__ cnt,
+                       const int32_t* __restrict__ pool, const uint32_t* __restrict__ leaf_idx, uint32_t n_leaf, double g,
+                       double margin_scale, uint32_t* __restrict__ Bbits, uint32_t* __restrict__ unc_list,
+                       uint32_t* __restrict__ unc_count) {
+    const uint32_t t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if ((t >> 3) >= n_leaf) return;
+    const uint32_t i = leaf_idx[t >> 3], o = t & 7;
+    const double xn = x[i] + g / 4 + (double)((o >> 2) & 1) * g / 2;
+    const double yn = y[i] + g / 2 + (double)((o >> 1) & 1) * g / 2;
+    const double zn = z[i] + g / 2 + (double)((o >> 0) & 1) * g / 2;
+    double B = 0, a = 0, s = 0;
+    const uint32_t first = off[i], count = cnt[i];
+    for (int pass = 0; pass < 2; pass++) {                       // all dipoles (+), then the leaf's residents (-)
+        const int total = pass == 0 ? n_mnp : (int)count;
+        for (int k0 = 0; k0 < total; k0 += 32) {
+            const int c = min(32, total - k0);
+            double term = 0.0;
+            if ((int)lane < c) {
+                const double4 m = mnp[pass == 0 ? k0 + (int)lane : pool[first + k0 + lane]];
+                const double dx = xn - m.x, dy = yn - m.y, dz = zn - m.z;
+                const double r2 = normsq(dx, dy, dz);
+                const double divisor = r2 * r2 * sqrt(r2);
+                term = m.w * 1e11 * (2 * dz * dz - dx * dx - dy * dy) / divisor;
+                a += fabs(term);
+            }
+            if (pass == 0) for (int j = 0; j < c; j++) { B += __shfl_sync(kFullMask, term, j); s += fabs(B); }
+            else           for (int j = 0; j < c; j++) { B -= __shfl_sync(kFullMask, term, j); s += fabs(B); }
+        }
+    }
+    a = warp_sum_d(a) * 1.000001;
+    if (lane) return;
+    const double e = (kRelTerm * a + kRelSum * s + 0x1p-51 * fabs(B)) * margin_scale;
+    const float lo = (float)(B - e), hi = (float)(B + e), Bf = (float)B;
+    const bool certain = isfinite(B) && isfinite(e) && (__float_as_uint(lo) == __float_as_uint(hi));
+    Bbits[(size_t)i * 8 + o] = __float_as_uint(Bf);
+    if (!certain) unc_list[atomicAdd(unc_count, 1u)] = i * 8 + o;
+}
+
 __global__ void flag_internal_kernel(const uint8_t* __restrict__ leaf, uint32_t n, uint32_t* __restrict__ is_int) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) is_int[i] = leaf[i] ? 0u : 1u;
@@ -392,8 +493,13 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         if (g < kMinG) {
             OB_CK(cudaMemsetAsync(d_leaf.p, 1, n, st));
         } else {
-            criterion_kernel<<<blocks_for(n), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g, grad_lim,
-                                                               kMaxProduct, margin_scale, d_leaf.p, d_unc.p, d_unc_count.p);
+            if (n <= kWarpNodes)
+                criterion_warp_kernel<<<blocks_for((uint64_t)n * 32), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g,
+                                                                                         grad_lim, kMaxProduct, margin_scale, d_leaf.p,
+                                                                                         d_unc.p, d_unc_count.p);
+            else
+                criterion_kernel<<<blocks_for(n), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g, grad_lim,
+                                                                   kMaxProduct, margin_scale, d_leaf.p, d_unc.p, d_unc_count.p);
             st_.kernel_launches++; st_.criterion_evals += n; st_.pair_evals += (uint64_t)n * (uint64_t)n_mnp;
         }
         OB_CK(cudaEventRecord(ev1, st));
@@ -429,9 +535,14 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         // ---- float B samples of the leaves (octree.cpp:272-298)
         OB_CK(cudaMemsetAsync(d_unc_count.p, 0, 4, st));
         if (n_leaf) {
-            leaf_field_kernel<<<blocks_for((uint64_t)n_leaf * 8), kThreads, 0, st>>>(
-                d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
-                margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
+            if ((uint64_t)n_leaf * 8 <= kWarpPoints)
+                leaf_field_warp_kernel<<<blocks_for((uint64_t)n_leaf * 8 * 32), kThreads, 0, st>>>(
+                    d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
+                    margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
+            else
+                leaf_field_kernel<<<blocks_for((uint64_t)n_leaf * 8), kThreads, 0, st>>>(
+                    d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
+                    margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
             st_.kernel_launches++; st_.b_values += (uint64_t)n_leaf * 8;
         }
 
