@@ -362,7 +362,7 @@ def main():
     # and the clock are measured live.
     issue = None
     mixf = os.path.join(ROOT, "profiles", "instr_mix_r01.json")
-    if os.path.exists(mixf) and args.field_mode == "exact" and clocks and clocks.get("sm_mhz"):
+    if os.path.exists(mixf) and args.field_mode == "exact" and clocks and clocks.get("sm_mhz") and not ctx.pipeline_sprints:
         try:
             mix = json.load(open(mixf))
             n_sm = torch.cuda.get_device_properties(local).multi_processor_count
@@ -392,7 +392,9 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
-                     "traffic": traffic, "kernel": "walker_sprint_kernel", "kernel_ms": k_ms,
+                     "traffic": traffic, "kernel_ms": k_ms,
+                     "kernel": "walker_sprint_kernel" if not ctx.pipeline_sprints else
+                               "pipelined path (walker_draws + walker_path + step_field + walker_phase kernels; kernel_ms is their sum)",
                      "algorithmic_fp64_ops_per_walker_step": F, "C_L_R": [Cbar, Lbar, Rbar], "issue": issue,
                      "peak_source": "measured live: mrisim_measure_fp64_tflops (8 independent DFMA chains/thread, all SMs); "
                                     "MEASURED_PEAKS.json has no FP64 entry",
