@@ -10,6 +10,7 @@
 // Here: level-synchronous breadth-first build.  Per level four data-parallel kernels
 //   criterion_kernel   one thread per node:  grad over all dipoles (sequential, reference order)
 //   leaf_field_kernel  one thread per (leaf, sample point): field over all dipoles - residents
+//                      (small levels: the *_group_kernel<G> variants, G lanes per point, further down)
 //   spawn_kernel       one thread per child of an internal node: corner, Morton code
 //   filter_kernel x2   count / fill the child's resident list from the parent's (order kept)
 // with CUB exclusive scans in between; nodes live in SoA arrays per level, resident lists are
@@ -176,29 +177,40 @@ leaf_field_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __re
 // and the running sums take them IN TABLE ORDER through shuffles -- the order is part of the result
 // (it is the host's `ret += ...`), so the values are those of the kernels above bit for bit.  The
 // sum|term| bound is order-free and is reduced at the end.  ~5x the issue slots per pair of the
-// thread-per-point kernels, so only used while a level is latency-bound (kWarpNodes / kWarpPoints).
-constexpr uint32_t kWarpNodes = 20000, kWarpPoints = 24000;
+// thread-per-point kernels, so only used while a level is latency-bound.
+// G = 32 lanes per point for the smallest levels, G = 4 for the levels in between (enough points to
+// fill the machine four lanes each, too few to hide a whole dipole walk per thread).
+// Measured on B200, 5190 dipoles: criterion 16 k nodes 2.2 ms (G=32) / 39 k nodes 2.6 -> 2.1 ms and 28 k nodes 2.4 -> 1.4 ms
+// (thread -> G=4); leaf field 89 k points 1.83 ms (thread) vs 2.06 ms (G=4), so no G=4 band there.
+constexpr uint32_t kWarpNodes = 6000, kWarpPoints = 24000;        // up to here: 32 lanes per point
+constexpr uint32_t kQuadNodes = 100000, kQuadPoints = 0;          // up to here: 4 lanes per point
 constexpr unsigned kFullMask = 0xffffffffu;
 
-__device__ __forceinline__ double warp_sum_d(double v) {
+template <int G>
+__device__ __forceinline__ double group_sum_d(double v) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
     return v;
 }
 
+template <int G>
 __global__ void __launch_bounds__(kThreads)
-criterion_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
-                      const double* __restrict__ z, uint32_t n, double g, double grad_lim, double max_prod, double margin_scale,
-                      uint8_t* __restrict__ leaf, uint32_t* __restrict__ unc_list, uint32_t* __restrict__ unc_count) {
-    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (i >= n) return;
+criterion_group_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
+                       const double* __restrict__ z, uint32_t n, double g, double grad_lim, double max_prod, double margin_scale,
+                       uint8_t* __restrict__ leaf, uint32_t* __restrict__ unc_list, uint32_t* __restrict__ unc_count) {
+    const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31, sub = lane & (G - 1), first = lane & ~(uint32_t)(G - 1);
+    if (((gt & ~31u) / G) >= n) return;                                  // whole warp past the end
+    const uint32_t node = gt / G;
+    const bool live = node < n;
+    const uint32_t i = live ? node : n - 1;                              // idle groups shadow the last node (they still take part in the shuffles)
     const double px = x[i] + g / 2, py = y[i] + g / 2, pz = z[i] + g / 2;
     double rx = 0, ry = 0, rz = 0, ax = 0, ay = 0, az = 0, sx = 0, sy = 0, sz = 0;
-    for (int k0 = 0; k0 < n_mnp; k0 += 32) {
-        const int cnt = min(32, n_mnp - k0);
+    for (int k0 = 0; k0 < n_mnp; k0 += G) {
+        const int cnt = min(G, n_mnp - k0);
         double tx = 0.0, ty = 0.0, tz = 0.0;
-        if ((int)lane < cnt) {
-            const double4 m = mnp[k0 + lane];
+        if ((int)sub < cnt) {
+            const double4 m = mnp[k0 + sub];
             const double dx = px - m.x, dy = py - m.y, dz = pz - m.z, M = m.w;
             const double r2 = normsq(dx, dy, dz);
             const bool on = r2 > grad_lim;
@@ -213,12 +225,12 @@ criterion_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* 
             ax += fabs(tx); ay += fabs(ty); az += fabs(tz);
         }
         for (int j = 0; j < cnt; j++) {
-            rx += __shfl_sync(kFullMask, tx, j); ry += __shfl_sync(kFullMask, ty, j); rz += __shfl_sync(kFullMask, tz, j);
+            rx += __shfl_sync(kFullMask, tx, first + j); ry += __shfl_sync(kFullMask, ty, first + j); rz += __shfl_sync(kFullMask, tz, first + j);
             sx += fabs(rx); sy += fabs(ry); sz += fabs(rz);
         }
     }
-    ax = warp_sum_d(ax) * 1.000001; ay = warp_sum_d(ay) * 1.000001; az = warp_sum_d(az) * 1.000001;
-    if (lane) return;
+    ax = group_sum_d<G>(ax) * 1.000001; ay = group_sum_d<G>(ay) * 1.000001; az = group_sum_d<G>(az) * 1.000001;
+    if (sub || !live) return;
     const double grad = sqrt(normsq(rx, ry, rz));
     const double lhs = g / 2 * 1e-6 * grad;
     const double ex = kRelTerm * ax + kRelSum * sx, ey = kRelTerm * ay + kRelSum * sy, ez = kRelTerm * az + kRelSum * sz;
@@ -230,14 +242,20 @@ criterion_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* 
     if (!certain) unc_list[atomicAdd(unc_count, 1u)] = i;
 }
 
+// G >= 4 and a multiple-of-8 point index per leaf: the 32/G points of a warp belong to ONE leaf, so the
+// resident count is uniform over the warp
+template <int G>
 __global__ void __launch_bounds__(kThreads)
-leaf_field_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
-                       const double* __restrict__ z, const uint32_t* __restrict__ off, const uint32_t* __restrict__ cnt,
-                       const int32_t* __restrict__ pool, const uint32_t* __restrict__ leaf_idx, uint32_t n_leaf, double g,
-                       double margin_scale, uint32_t* __restrict__ Bbits, uint32_t* __restrict__ unc_list,
-                       uint32_t* __restrict__ unc_count) {
-    const uint32_t t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if ((t >> 3) >= n_leaf) return;
+leaf_field_group_kernel(const double4* __restrict__ mnp, int n_mnp, const double* __restrict__ x, const double* __restrict__ y,
+                        const double* __restrict__ z, const uint32_t* __restrict__ off, const uint32_t* __restrict__ cnt,
+                        const int32_t* __restrict__ pool, const uint32_t* __restrict__ leaf_idx, uint32_t n_leaf, double g,
+                        double margin_scale, uint32_t* __restrict__ Bbits, uint32_t* __restrict__ unc_list,
+                        uint32_t* __restrict__ unc_count) {
+    static_assert(G >= 4 && G <= 32, "a warp must stay within one leaf");
+    const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31, sub = lane & (G - 1), first_lane = lane & ~(uint32_t)(G - 1);
+    const uint32_t t = gt / G;                                            // sample point
+    if ((t >> 3) >= n_leaf) return;                                      // uniform over the warp
     const uint32_t i = leaf_idx[t >> 3], o = t & 7;
     const double xn = x[i] + g / 4 + (double)((o >> 2) & 1) * g / 2;
     const double yn = y[i] + g / 2 + (double)((o >> 1) & 1) * g / 2;
@@ -246,23 +264,23 @@ leaf_field_warp_kernel(const double4* __restrict__ mnp, int n_mnp, const double*
     const uint32_t first = off[i], count = cnt[i];
     for (int pass = 0; pass < 2; pass++) {                       // all dipoles (+), then the leaf's residents (-)
         const int total = pass == 0 ? n_mnp : (int)count;
-        for (int k0 = 0; k0 < total; k0 += 32) {
-            const int c = min(32, total - k0);
+        for (int k0 = 0; k0 < total; k0 += G) {
+            const int c = min(G, total - k0);
             double term = 0.0;
-            if ((int)lane < c) {
-                const double4 m = mnp[pass == 0 ? k0 + (int)lane : pool[first + k0 + lane]];
+            if ((int)sub < c) {
+                const double4 m = mnp[pass == 0 ? k0 + (int)sub : pool[first + k0 + sub]];
                 const double dx = xn - m.x, dy = yn - m.y, dz = zn - m.z;
                 const double r2 = normsq(dx, dy, dz);
                 const double divisor = r2 * r2 * sqrt(r2);
                 term = m.w * 1e11 * (2 * dz * dz - dx * dx - dy * dy) / divisor;
                 a += fabs(term);
             }
-            if (pass == 0) for (int j = 0; j < c; j++) { B += __shfl_sync(kFullMask, term, j); s += fabs(B); }
-            else           for (int j = 0; j < c; j++) { B -= __shfl_sync(kFullMask, term, j); s += fabs(B); }
+            if (pass == 0) for (int j = 0; j < c; j++) { B += __shfl_sync(kFullMask, term, first_lane + j); s += fabs(B); }
+            else           for (int j = 0; j < c; j++) { B -= __shfl_sync(kFullMask, term, first_lane + j); s += fabs(B); }
         }
     }
-    a = warp_sum_d(a) * 1.000001;
-    if (lane) return;
+    a = group_sum_d<G>(a) * 1.000001;
+    if (sub) return;
     const double e = (kRelTerm * a + kRelSum * s + 0x1p-51 * fabs(B)) * margin_scale;
     const float lo = (float)(B - e), hi = (float)(B + e), Bf = (float)B;
     const bool certain = isfinite(B) && isfinite(e) && (__float_as_uint(lo) == __float_as_uint(hi));
@@ -494,9 +512,13 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
             OB_CK(cudaMemsetAsync(d_leaf.p, 1, n, st));
         } else {
             if (n <= kWarpNodes)
-                criterion_warp_kernel<<<blocks_for((uint64_t)n * 32), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g,
-                                                                                         grad_lim, kMaxProduct, margin_scale, d_leaf.p,
-                                                                                         d_unc.p, d_unc_count.p);
+                criterion_group_kernel<32><<<blocks_for((uint64_t)n * 32), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g,
+                                                                                              grad_lim, kMaxProduct, margin_scale, d_leaf.p,
+                                                                                              d_unc.p, d_unc_count.p);
+            else if (n <= kQuadNodes)
+                criterion_group_kernel<4><<<blocks_for((uint64_t)n * 4), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g,
+                                                                                            grad_lim, kMaxProduct, margin_scale, d_leaf.p,
+                                                                                            d_unc.p, d_unc_count.p);
             else
                 criterion_kernel<<<blocks_for(n), kThreads, 0, st>>>(d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, n, g, grad_lim,
                                                                    kMaxProduct, margin_scale, d_leaf.p, d_unc.p, d_unc_count.p);
@@ -535,12 +557,17 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         // ---- float B samples of the leaves (octree.cpp:272-298)
         OB_CK(cudaMemsetAsync(d_unc_count.p, 0, 4, st));
         if (n_leaf) {
-            if ((uint64_t)n_leaf * 8 <= kWarpPoints)
-                leaf_field_warp_kernel<<<blocks_for((uint64_t)n_leaf * 8 * 32), kThreads, 0, st>>>(
+            const uint64_t n_pts = (uint64_t)n_leaf * 8;
+            if (n_pts <= kWarpPoints)
+                leaf_field_group_kernel<32><<<blocks_for(n_pts * 32), kThreads, 0, st>>>(
+                    d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
+                    margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
+            else if (n_pts <= kQuadPoints)
+                leaf_field_group_kernel<4><<<blocks_for(n_pts * 4), kThreads, 0, st>>>(
                     d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
                     margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
             else
-                leaf_field_kernel<<<blocks_for((uint64_t)n_leaf * 8), kThreads, 0, st>>>(
+                leaf_field_kernel<<<blocks_for(n_pts), kThreads, 0, st>>>(
                     d_mnp.p, n_mnp, cur.x.p, cur.y.p, cur.z.p, cur.off.p, cur.cnt.p, cur.pool.p, d_leaf_idx.p, n_leaf, g,
                     margin_scale, d_Bbits.p, d_unc.p, d_unc_count.p);
             st_.kernel_launches++; st_.b_values += (uint64_t)n_leaf * 8;

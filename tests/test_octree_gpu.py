@@ -34,6 +34,17 @@ def test_refuses_without_a_device():
         api.BacteriaBox(p, 3).populateSimulation(device=63)
 
 
+def test_gpu_rethrow_refuses_without_a_device():
+    p = api.ParameterStruct(**KATS["configs"]["tiny"])
+    box = api.BacteriaBox(p, 3).populateSimulation()
+    before = box.getWaters().tobytes()
+    with pytest.raises(api.MrisimError, match="no CUDA device|CUDA|cuda"):
+        box.rethrow_waters(100, 5, device=63)
+    with pytest.raises(api.MrisimError, match="device must be >= 0"):
+        box.rethrow_waters(100, 5, device=-1)
+    assert box.getWaters().tobytes() == before          # a refused call leaves the scene alone
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("cfg,seed", [("tiny", 3), ("default", 12345)])
 def test_gpu_build_byte_identical_to_reference_dump(cfg, seed, tmp_path):
