@@ -79,10 +79,19 @@ def make_params(api, name):
     return p, seed, n
 
 
-def get_scene(api, name, rank, world, barrier):
-    """Rank 0 builds the scene once (host octree build: ~15 s for 2000 cells on 8 cores) and
-    saves it; the other ranks load the file."""
+def get_scene(api, name, rank, world, barrier, device=None):
+    """The workload's scene.  device=None (the CPU reference arm): rank 0 builds it with the host
+    threads once (~3 s for 2000 cells on 16 cores) and saves it, the other ranks load the file.
+    device=k (our arm): every rank builds it on its own GPU (csrc/octree_build.cu, byte-identical
+    to the host build, ~50 ms) -- no file, no barrier."""
     p, seed, n = make_params(api, name)
+    if device is not None:
+        t = time.time()
+        q = p.copy(); q.num_water = 64
+        box = api.BacteriaBox(q, seed).populateSimulation(device=device)
+        if rank == 0:
+            log(f"[bench] scene {name} built on the GPU in {time.time() - t:.2f} s")
+        return box, p, n
     path = f"/tmp/mrisim_bench_{name}_seed{seed}.scn"
     if rank == 0 and not os.path.exists(path):
         t = time.time()
@@ -95,9 +104,10 @@ def get_scene(api, name, rank, world, barrier):
     return box, p, n
 
 
-def throw_waters(box, p, n, rank):
-    """This rank's walkers: BacteriaBox::init_waters + sortWaters from XORShift(7000 + rank)."""
-    box.rethrow_waters(n, 7000 + rank, True, p)
+def throw_waters(box, p, n, rank, device=None):
+    """This rank's walkers: BacteriaBox::init_waters + sortWaters from XORShift(7000 + rank);
+    on the GPU for our arm (csrc/scene_gpu.cu, same bytes)."""
+    box.rethrow_waters(n, 7000 + rank, True, p, device=device)
     return box.getWaters().copy()
 
 
@@ -269,10 +279,10 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
 
-    box, p, n_per_gpu = get_scene(api, args.workload, rank, world, barrier)
+    box, p, n_per_gpu = get_scene(api, args.workload, rank, world, barrier, device=local)
     if args.walkers_per_gpu:
         n_per_gpu = args.walkers_per_gpu
-    waters = throw_waters(box, p, n_per_gpu, rank)
+    waters = throw_waters(box, p, n_per_gpu, rank, device=local)
     steps = p.sprintSteps
     n_int = steps // p.pfreq
     ctx = api.WalkerContext(p, local)
