@@ -1,4 +1,5 @@
-mkdir -p gpurun_out/v17
-(time python bench.py --steps 3 --warmup 3) > gpurun_out/v17/bench.json 2> gpurun_out/v17/bench.err; echo "exit $?"; head -c 600 gpurun_out/v17/bench.json; echo; grep -v "^$" gpurun_out/v17/bench.err | tail -8
-(time python bench.py --workload cfg1_default_4032_waters --steps 3 --warmup 3 --no-cpu-baseline) > gpurun_out/v17/bench_cfg1.json 2> gpurun_out/v17/bench_cfg1.err; head -c 300 gpurun_out/v17/bench_cfg1.json; echo; tail -5 gpurun_out/v17/bench_cfg1.err
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/v17/bench_2gpu.json 2> gpurun_out/v17/bench2.err; echo "bench2 exit $?"; wc -l gpurun_out/v17/bench_2gpu.json; head -c 200 gpurun_out/v17/bench_2gpu.json
+mkdir -p gpurun_out/san
+python scripts/sanitize_case.py > gpurun_out/san/plain.log 2>&1; echo "plain exit $?"; tail -3 gpurun_out/san/plain.log
+timeout 900 compute-sanitizer --tool memcheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/memcheck.log 2>&1; echo "memcheck exit $?"; tail -4 gpurun_out/san/memcheck.log
+timeout 900 compute-sanitizer --tool racecheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/racecheck.log 2>&1; echo "racecheck exit $?"; tail -4 gpurun_out/san/racecheck.log
+timeout 900 compute-sanitizer --tool synccheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/synccheck.log 2>&1; echo "synccheck exit $?"; tail -3 gpurun_out/san/synccheck.log
