@@ -1,5 +1,4 @@
-mkdir -p gpurun_out/san
-python scripts/sanitize_case.py > gpurun_out/san/plain.log 2>&1; echo "plain exit $?"; tail -3 gpurun_out/san/plain.log
-timeout 900 compute-sanitizer --tool memcheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/memcheck.log 2>&1; echo "memcheck exit $?"; tail -4 gpurun_out/san/memcheck.log
-timeout 900 compute-sanitizer --tool racecheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/racecheck.log 2>&1; echo "racecheck exit $?"; tail -4 gpurun_out/san/racecheck.log
-timeout 900 compute-sanitizer --tool synccheck --error-exitcode 7 python scripts/sanitize_case.py > gpurun_out/san/synccheck.log 2>&1; echo "synccheck exit $?"; tail -3 gpurun_out/san/synccheck.log
+mkdir -p gpurun_out/xc
+export MRISIM_XCHECK_OUT=$PWD/gpurun_out/xc
+(time timeout 1500 python -m pytest tests/test_ref_gpu_crosscheck.py -m gpu -x -q -rP 2>&1 | grep -v "^$" | tail -30) > gpurun_out/xc/pytest.log 2>&1; grep -E "reference GPU code|passed|failed|Error|assert" gpurun_out/xc/pytest.log | cut -c1-400; tail -4 gpurun_out/xc/pytest.log
+ls gpurun_out/xc
