@@ -24,7 +24,8 @@ HOST_SEED = 12345
 # name -> (waters, sprintSteps, totaltime ms) = GCFG_<name> in oracle/Makefile
 #   xcheck : many waters, short (one CPMG flip)            -> tight Monte-Carlo bound
 #   default: the SHIPPED parameters.h, the whole 40 ms run -> BASELINE configs[0] end to end, 7 flips, 40 000 rows
-RUNS = {"xcheck": (65536, 2000, 6), "default": (4032, 20000, 40)}
+#   cfg3   : BASELINE configs[2]: low-permeability membranes (parameters.h:116-117), 100 000 waters -> the reflection rule
+RUNS = {"xcheck": (65536, 2000, 6), "default": (4032, 20000, 40), "cfg3": (100000, 4000, 10)}
 
 
 def read_csv(path):
@@ -34,9 +35,12 @@ def read_csv(path):
 
 @pytest.mark.gpu
 @pytest.mark.slow
-@pytest.mark.parametrize("run", ["xcheck", "default"])
+@pytest.mark.parametrize("run", ["xcheck", "default", "cfg3"])
 def test_t2_signal_agrees_with_reference_gpu_code(run, tmp_path):
     N, SPRINT, TOTALTIME_MS = RUNS[run]
+    if run != "xcheck" and os.environ.get("MRISIM_LONG_XCHECK") != "1":
+        pytest.skip("3-4 minutes of GPU time each (the reference binary is the slow side): set MRISIM_LONG_XCHECK=1; "
+                    "last recorded results in profiles/ref_gpu_crosscheck_r01.txt and profiles/t2_curves_*.csv")
     EXE = os.path.join(REF, f"ref_gpu_{run}")
     if not os.path.exists(EXE):
         pytest.skip(f"oracle/_ref/ref_gpu_{run} not built (make -C oracle refgpu needs /root/reference)")
@@ -48,6 +52,9 @@ def test_t2_signal_agrees_with_reference_gpu_code(run, tmp_path):
     ref_ms = float(m.group(1))
 
     p = api.ParameterStruct(num_water=N, sprintSteps=SPRINT, totaltime=TOTALTIME_MS)
+    if run == "cfg3":
+        api.low_permeability(p)
+        assert (p.reflectIO, p.reflectOI) == (0.999561484166706, 0.9997468303722928)
     assert p.t == TOTALTIME_MS * 1_000_000 and p.tcp == 5_500_000 and p.pfreq == 1000
     import time
     t0 = time.perf_counter()
