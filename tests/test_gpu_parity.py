@@ -107,6 +107,28 @@ def test_pipelined_path_bit_exact(name, field_mode):
     assert np.max(np.abs(sig - osig)) / len(w0) <= SIGNAL_TOL
 
 
+@pytest.mark.parametrize("n", [16384, 30000])
+def test_pipelined_path_mid_sizes_equal_fused(n):
+    """Walker counts where the pipelined path picks draw-chunks that are NOT a multiple of its 8-step
+    store tile (50 steps at 16 Ki walkers) and cuts a sprint into several launch groups: every walker
+    and RNG state must equal the fused path's (which the other tests pin to the oracle), low-permeability
+    membranes with walkers starting inside cells so that crossings end speculative trips."""
+    p = api.low_permeability(api.ParameterStruct(avoid_intracellular_throw=0))
+    box, _ = make(p, 12345)
+    box.rethrow_waters(n, 99, True, p)
+    w0 = box.getWaters().copy()
+    out = []
+    for mode in (api.PATH_PIPELINE, api.PATH_FUSED):
+        ctx = gpu_ctx(p, box, w0)
+        ctx.set_path_mode(mode)
+        sig = np.concatenate([ctx.run_sprint(3000), ctx.run_sprint(1000)])
+        out.append((ctx.get_waters(), ctx.get_rng(), sig, ctx.pipeline_sprints))
+    assert out[0][3] == 2 and out[1][3] == 0
+    assert out[0][0].tobytes() == out[1][0].tobytes() and out[0][1].tobytes() == out[1][1].tobytes()
+    assert np.max(np.abs(out[0][2] - out[1][2])) <= 1e-9 * n
+    assert int(out[0][0]["in_cell"].sum()) > 0
+
+
 def test_path_mode_auto_and_fallbacks():
     """AUTO takes the pipelined path for few walkers and the fused one for many, for traces, and for
     sprints that do not start on an even step; mixing the paths sprint by sprint changes no walker."""
