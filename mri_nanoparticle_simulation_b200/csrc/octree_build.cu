@@ -85,7 +85,7 @@ struct HostLevel {
     std::vector<double> x, y, z;
     std::vector<uint64_t> mc;
     std::vector<uint8_t> leaf;
-    std::vector<uint32_t> off, cnt, int_rank, Bbits;
+    std::vector<uint32_t> off, cnt, int_rank, Bbits, out_index;   // out_index: leaf -> node index in the linearised forest
     std::vector<int32_t> pool;
 };
 
@@ -391,9 +391,12 @@ static cudaError_t exclusive_sum(const uint32_t* in, uint32_t* out, uint32_t n, 
     return cub::DeviceScan::ExclusiveSum(tmp.p, bytes, in, out, (int)n, st);
 }
 
-static void emit_subtree(const std::vector<HostLevel>& lv, const std::vector<mrisim_mnp>& mnps, size_t d, uint32_t i,
+// The float samples of the leaves are NOT read here (the libm fix-up threads may still be patching
+// them): each leaf's position in the output is recorded in out_index and the samples are copied
+// once the fix-ups have been joined.
+static void emit_subtree(std::vector<HostLevel>& lv, const std::vector<mrisim_mnp>& mnps, size_t d, uint32_t i,
                          OctreeOut& out) {
-    const HostLevel& L = lv[d];
+    HostLevel& L = lv[d];
     const size_t self = out.nodes.size();
     mrisim_node nd;
     std::memset(&nd, 0, sizeof nd);
@@ -402,7 +405,7 @@ static void emit_subtree(const std::vector<HostLevel>& lv, const std::vector<mri
     if (L.leaf[i]) {
         nd.mc |= (1ULL << 63);
         nd.n_res = L.cnt[i];
-        for (int o = 0; o < 8; o++) nd.child[o] = L.Bbits[(size_t)i * 8 + o];
+        L.out_index[i] = (uint32_t)self;
         out.nodes.push_back(nd);
         for (uint32_t k = 0; k < L.cnt[i]; k++) out.residents.push_back(mnps[(size_t)L.pool[L.off[i] + k]]);
         return;
@@ -646,23 +649,27 @@ int build_octree_gpu(const mrisim_params& p, const std::vector<mrisim_mnp>& mnps
         g = gc;
     }
 
-    {   // the libm re-evaluations still running: wait (only this part of them is on the critical path)
-        const double t0 = now_ms();
-        fixers.join();
-        st_.fixup_wait_ms = now_ms() - t0;
-        st_.fixup_ms = fix_ms.load();
-    }
-    // ---- depth-first linearisation (octree.cpp:303-322 order), subtree by subtree
+    // ---- depth-first linearisation (octree.cpp:303-322 order), subtree by subtree, beside the fix-up threads
     const double t_lin = now_ms();
     out.subtree_sizes.assign(n_roots, 0);
     out.nodes.clear(); out.residents.clear();
     out.nodes.reserve(st_.n_nodes);
+    for (HostLevel& L : levels) L.out_index.assign(L.n, 0xffffffffu);
     for (uint32_t r = 0; r < n_roots; r++) {
         const size_t before = out.nodes.size();
         emit_subtree(levels, mnps, 0, r, out);
         out.subtree_sizes[r] = (uint32_t)(out.nodes.size() - before);
     }
     st_.linearise_ms = now_ms() - t_lin;
+    {   // the libm re-evaluations still running: wait (only this part of them is on the critical path)
+        const double t0 = now_ms();
+        fixers.join();
+        st_.fixup_wait_ms = now_ms() - t0;
+        st_.fixup_ms = fix_ms.load();
+    }
+    for (const HostLevel& L : levels)                      // the (now final) float samples of every leaf
+        for (uint32_t i = 0; i < L.n; i++)
+            if (L.leaf[i]) std::memcpy(out.nodes[L.out_index[i]].child, &L.Bbits[(size_t)i * 8], 8 * sizeof(uint32_t));
     st_.total_ms = now_ms() - t_begin;
     if (stats) *stats = st_;
     return 0;
