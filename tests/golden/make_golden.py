@@ -28,7 +28,8 @@ from mri_nanoparticle_simulation_b200 import scene_io as sio  # noqa: E402
 
 REF = os.path.join(ROOT, "oracle", "_ref")
 FULL = [("tiny", 3), ("default", 12345)]                  # committed as whole files
-HASHED = [("default", 7), ("noavoid", 99), ("n8000", 5), ("n8000_noavoid", 21), ("dense2000", 11)]
+HASHED = [("default", 7), ("noavoid", 99), ("n8000", 5), ("n8000_noavoid", 21), ("dense2000", 11),
+          ("dense8000", 11)]          # the last one is minutes of host time in the reference's octree constructor
 #: how each config differs from the shipped parameters.h (mirrors oracle/Makefile CFG_*)
 CONFIGS = {
     "default": {},
@@ -37,6 +38,7 @@ CONFIGS = {
     "n8000_noavoid": {"num_water": 8000, "avoid_intracellular_throw": 0},
     "tiny": {"num_water": 256, "num_cells": 40, "bound": 10, "water_start_bound": 6, "hashDim": 8, "border": 3},
     "dense2000": {"num_water": 4096, "num_cells": 2000, "hashDim": 40, "maxNeighbors": 16},
+    "dense8000": {"num_water": 4096, "num_cells": 8000, "hashDim": 40, "maxNeighbors": 32},
 }
 
 
