@@ -26,7 +26,7 @@ EXE = os.path.join(PKG, "gpu_sim.out")
 # octree indices bit-identical to the oracle (see include/mrisim_math.h)
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
               "-fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", INC] + \
-             [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK", "MRISIM_TERMS_PER_TRIP") if os.environ.get(k)]
+             [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK") if os.environ.get(k)]
 CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC]
 
 CU_SOURCES = ["mrisim.cu", "octree_build.cu", "scene_gpu.cu"]

@@ -1,7 +1,3 @@
-out=gpurun_out/v27; mkdir -p $out
-(timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4) > $out/pytest_gpu.txt; cat $out/pytest_gpu.txt
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $out/smoke.log 2>&1; tail -1 $out/smoke.log
-timeout 600 python scripts/crossover.py 4032 16384 32768 49152 65536 98304 > $out/crossover.json 2> $out/crossover.err; grep -c walkers $out/crossover.json
-python bench.py --workload cfg1_default_4032_waters --no-cpu-baseline > $out/bench_cfg1.json 2> $out/bench_cfg1.err; cut -c1-200 $out/bench_cfg1.json
-python bench.py --workload cfg2_8000_waters_intracellular_kick --no-cpu-baseline > $out/bench_cfg2.json 2> $out/bench_cfg2.err; cut -c1-200 $out/bench_cfg2.json
-python bench.py > $out/bench.json 2> $out/bench.err; cut -c1-200 $out/bench.json
+out=gpurun_out/v28; mkdir -p $out
+MRISIM_LONG_XCHECK=1 MRISIM_XCHECK_OUT=$out timeout 900 python -m pytest tests/test_ref_gpu_crosscheck.py -m gpu -x -q -rP -k "default" 2>&1 | grep -v "^$" | tail -25 | cut -c1-400 > $out/xcheck_default.txt; cat $out/xcheck_default.txt
+timeout 300 python scripts/crossover.py 40960 49152 57344 > $out/crossover2.json 2> $out/crossover2.err; grep -c walkers $out/crossover2.json

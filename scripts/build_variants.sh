@@ -3,7 +3,7 @@
 cd "$(dirname "$0")/.."
 for cfg in "$@"; do
   IFS=: read u b m <<< "$cfg"
-  MRISIM_TERMS_PER_TRIP=$u MRISIM_BLOCK=$b MRISIM_MIN_BLOCKS=$m MRISIM_LIB_SUFFIX=_u${u}b${b}m${m} python -m mri_nanoparticle_simulation_b200.build > /dev/null 2>&1 &
+  MRISIM_BLOCK=$b MRISIM_MIN_BLOCKS=$m MRISIM_LIB_SUFFIX=_u${u}b${b}m${m} python -m mri_nanoparticle_simulation_b200.build > /dev/null 2>&1 &
 done
 wait
 ls mri_nanoparticle_simulation_b200/*.so
