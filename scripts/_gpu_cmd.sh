@@ -1,5 +1,3 @@
-out=gpurun_out/v33; mkdir -p $out
-export WORKLOAD=cfg1_default_4032_waters
-(timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "pipelin or path_mode or cfg1" 2>&1 | tail -3) > $out/pytest_pipe.log; cat $out/pytest_pipe.log
-timeout 600 python scripts/profile_case.py 4032 20000 1 > $out/plain.log 2>&1; tail -3 $out/plain.log
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"walker_|step_field|chunk_s" -s 48 -c 48 --csv --log-file $out/launches_pipe.csv python scripts/profile_case.py 4032 20000 1 > /dev/null 2>&1
+out=gpurun_out/v34; mkdir -p $out
+(timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -4) > $out/pytest_gpu.txt; cat $out/pytest_gpu.txt
+timeout 60 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $out/smoke.log 2>&1; tail -1 $out/smoke.log
