@@ -257,6 +257,10 @@ void* mrisim_ctx_stream(mrisim_ctx* ctx);     /* the cudaStream_t the synchronou
  * are HOST memory, step-major [steps][n]; any pointer may be NULL. */
 int  mrisim_trace_sprint(mrisim_ctx* ctx, int32_t steps, double* signal_out,
                          double* x, double* y, double* z, uint8_t* in_cell, uint32_t* leaf);
+/* Same, plus the per-(step, walker) phase kick -- what computePhaseAccumulation writes into its
+ * target buffer (cuda_sim.cu:772-804, accumulatePhase :625-640) before the dgemv sums it. */
+int  mrisim_trace_sprint_kicks(mrisim_ctx* ctx, int32_t steps, double* signal_out,
+                               double* x, double* y, double* z, uint8_t* in_cell, uint32_t* leaf, double* kick);
 
 /* kernels launched by this context so far (bench.py's gpu_launches claim) */
 uint64_t mrisim_kernel_launches(const mrisim_ctx* ctx);

@@ -81,6 +81,7 @@ def lib():
         "mrisim_run_sprint_async": (C.c_int, [vp, i32, vp, vp]),
         "mrisim_ctx_stream": (vp, [vp]),
         "mrisim_trace_sprint": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp]),
+        "mrisim_trace_sprint_kicks": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp, vp]),
         "mrisim_kernel_launches": (u64, [vp]),
         "mrisim_last_sprint_kernel_ms": (C.c_float, [vp]),
         "mrisim_csv_row": (C.c_int, [i64, dbl, dbl, C.c_char_p, C.c_size_t]),
@@ -107,7 +108,7 @@ ABI_SYMBOLS = [
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
-    "mrisim_trace_sprint", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
+    "mrisim_trace_sprint", "mrisim_trace_sprint_kicks", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
     "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index",
 ]
 
@@ -346,13 +347,16 @@ class WalkerContext:
         CUDA's legacy default stream)."""
         self._ck(lib().mrisim_run_sprint_async(self._h, steps, signal_dev_ptr, stream))
 
-    def trace_sprint(self, steps: int):
+    def trace_sprint(self, steps: int, kicks: bool = False):
         n = self.n
         sig = np.zeros(steps // self.params.pfreq, dtype=np.float64)
         tr = dict(x=np.zeros((steps, n)), y=np.zeros((steps, n)), z=np.zeros((steps, n)),
                   in_cell=np.zeros((steps, n), np.uint8), leaf=np.zeros((steps, n), np.uint32))
-        self._ck(lib().mrisim_trace_sprint(self._h, steps, sig.ctypes.data, tr["x"].ctypes.data, tr["y"].ctypes.data,
-                                           tr["z"].ctypes.data, tr["in_cell"].ctypes.data, tr["leaf"].ctypes.data))
+        if kicks:
+            tr["kick"] = np.zeros((steps, n))
+        self._ck(lib().mrisim_trace_sprint_kicks(self._h, steps, sig.ctypes.data, tr["x"].ctypes.data, tr["y"].ctypes.data,
+                                                 tr["z"].ctypes.data, tr["in_cell"].ctypes.data, tr["leaf"].ctypes.data,
+                                                 tr["kick"].ctypes.data if kicks else None))
         return sig, tr
 
     @property

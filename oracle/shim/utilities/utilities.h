@@ -27,6 +27,11 @@
         }                                                                                     \
     } while (0)
 
+// Optional observers (defined by shim/gpu_random_contract.cu in the bit-pinning builds, absent
+// otherwise): which device arrays the reference allocated, and when its sprint loop ended.
+extern "C" void ref_shim_note_array(void* ptr, size_t n, size_t elem) __attribute__((weak));
+extern "C" void ref_shim_sprint_loop_done() __attribute__((weak));
+
 inline void* cudaAllocate(size_t bytes) {
     void* p = nullptr;
     HANDLE_ERROR(cudaMalloc(&p, bytes ? bytes : 1));
@@ -41,7 +46,9 @@ public:
     void cpuStart() { t0_ = std::chrono::steady_clock::now(); }
     float cpuStop() {
         cudaDeviceSynchronize();
-        return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0_).count();
+        const float ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0_).count();
+        if (ref_shim_sprint_loop_done) ref_shim_sprint_loop_done();      // cuda_sim.cu:1027 follows the sprint loop
+        return ms;
     }
 private:
     std::chrono::steady_clock::time_point t0_;
@@ -62,7 +69,9 @@ public:
 template <typename T>
 class d_array {                                 // device-only array, freed on scope exit
 public:
-    explicit d_array(size_t n) : n_(n), d_(static_cast<T*>(cudaAllocate(n * sizeof(T)))) {}
+    explicit d_array(size_t n) : n_(n), d_(static_cast<T*>(cudaAllocate(n * sizeof(T)))) {
+        if (ref_shim_note_array) ref_shim_note_array((void*)d_, n, sizeof(T));
+    }
     d_array(size_t n, T*& dev_out) : d_array(n) { dev_out = d_; }
     ~d_array() { cudaFree(d_); }
     d_array(const d_array&) = delete;
@@ -79,7 +88,10 @@ class p_array {                                 // host array paired with a devi
 public:
     explicit p_array(size_t n) : n_(n), h_(new T[n]()), own_(true), d_(static_cast<T*>(cudaAllocate(n * sizeof(T)))) {}
     p_array(size_t n, T* host_src, T*& dev_out)
-        : n_(n), h_(host_src), own_(false), d_(static_cast<T*>(cudaAllocate(n * sizeof(T)))) { dev_out = d_; }
+        : n_(n), h_(host_src), own_(false), d_(static_cast<T*>(cudaAllocate(n * sizeof(T)))) {
+        dev_out = d_;
+        if (ref_shim_note_array) ref_shim_note_array((void*)d_, n, sizeof(T));
+    }
     ~p_array() { cudaFree(d_); if (own_) delete[] h_; }
     p_array(const p_array&) = delete;
     p_array& operator=(const p_array&) = delete;

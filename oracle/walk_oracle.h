@@ -11,13 +11,26 @@
  * from the product is the walker stream contract (include/mrisim_math.h) that replaces the
  * irreproducible cuRAND stream.
  *
- * Pinning: the reference ships no golden vectors for this path and its
- * device half cannot run without cuRAND's wall-clock-seeded stream, so the WALK is
- * "parity unpinned" in the strict sense; what IS pinned is everything the walk consumes:
- * the scene arrays come from the reference's own host code (oracle/_ref, reproducing the
- * survey-time known answers of SURVEY.md A.6), the xoroshiro128+ words are checked against
- * the A.6 vectors, and the host-side traversal below is checked against the reference's
- * Octree::get_voxel / get_field outputs (tests/golden/field_probes_*.json).
+ * Pinning.  The reference ships no golden vectors for this path, so the pin is the
+ * reference ITSELF, run on the GPU box: oracle/_ref/ref_gpu_pin_<cfg> is the reference's unchanged
+ * cuda_sim.cu (its kernels, cuBLAS dgemv, thrust::reduce, CSV line) compiled where it lies with
+ * -fmad=false and linked with oracle/shim/gpu_random_contract.cu, which replaces only the 72-line
+ * cuRAND wrapper (src/gpu_random.cu) by a filler that writes the walker stream contract into the
+ * reference's own random buffers.  tests/test_ref_gpu_bitpin.py asserts, for three configurations,
+ * that per-(step, walker) positions, membrane flags and phase kicks of this oracle, of the product
+ * and of the reference's kernels are BIT-EQUAL, that the final walker state after 10^6 steps is
+ * bit-equal (phases to 1e-9 rad: cuBLAS owns the dgemv summation order) and that the CSV rows print
+ * identically (profiles/pytest_gpu_r02_bitpin_vs_reference_kernels.txt).  The scene arrays the walk
+ * consumes come from the reference's own host code (oracle/_ref, SURVEY.md A.6 known answers), and
+ * the host-side traversal below is also checked against the reference's Octree::get_voxel /
+ * get_field outputs (tests/golden/probes_*.json).
+ *
+ * What remains a CONTRACT rather than a pin: the reference draws from cuRAND XORWOW seeded with
+ * time(NULL) and has no reproducible stream; the contract (include/mrisim_math.h) substitutes the
+ * reference's own src/xorshift.h generator per walker and a Box-Muller convention of its own
+ * (pair drawn at even steps, v = 1 - u1, z0 = r*cos used first).  The xoroshiro/splitmix words are
+ * pinned to src/xorshift.h (A.6 vectors; the shim's self-check against the XORShift class); the
+ * Box-Muller convention is pinned by nothing but itself -- it is the definition of the stream.
  */
 #ifndef WALK_ORACLE_H
 #define WALK_ORACLE_H
