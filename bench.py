@@ -42,8 +42,14 @@ WORKLOADS = {
     "cfg2_8000_waters_intracellular_kick": (dict(num_water=8000, avoid_intracellular_throw=0), 21, 8000),
     "cfg3_lowperm_100k_waters": (dict(), 12345, 100000),
     "default_scene_1Mi_waters_per_gpu": (dict(), 12345, 1 << 20),
+    # SURVEY.md 8d "4b": 8000 cells (21 385 dipoles, 455 008 octree nodes, up to 104 residents per leaf)
+    "cfg4b_dense8000cells_1Mi_waters_per_gpu": (dict(num_cells=8000, hashDim=40, maxNeighbors=32), 11, 1 << 20),
+    # BASELINE configs[4]: 16 Mi waters IN TOTAL, split over the ranks (strong scaling), shipped scene
+    "cfg5_16Mi_waters_total": (dict(), 12345, 16 << 20),
 }
+STRONG = {"cfg5_16Mi_waters_total"}          # the walker count is the job's, not the rank's
 DEFAULT_WORKLOAD = "cfg4a_dense2000cells_1Mi_waters_per_gpu"
+SMALL_CONFIGS = ("cfg1_default_4032_waters", "cfg2_8000_waters_intracellular_kick")     # the reference's shipped sizes
 WALKER_SEED = 0xC0FFEE
 
 
@@ -192,10 +198,10 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------
-def cpu_arm(api, ol, box, p, waters, budget_s, n_threads, steps):
+def cpu_arm(make_oracle, p, waters, budget_s, n_threads, steps):
     """Time the oracle port (CPU restatement of the reference's device functions; the
     reference has no CPU walk of its own) on a bounded walker sample."""
-    orc = ol.oracle_for_box(box, p)
+    orc = make_oracle()
     calib_n = min(len(waters), 64 * n_threads)
     w = waters[:calib_n].copy(); rng = orc.seed(calib_n, WALKER_SEED)
     t = time.perf_counter(); orc.run_sprint(w, rng, 0, p.pfreq, n_threads=n_threads); dt = time.perf_counter() - t
@@ -206,16 +212,75 @@ def cpu_arm(api, ol, box, p, waters, budget_s, n_threads, steps):
     return orc, n, rate
 
 
-def run_reference_arm(args, api, ol):
+def shipped_params(cabi, **over):
+    """The shipped src/parameters.h as an mrisim_params, filled in Python: the reference arm must not load
+    the product library.  tests/test_bench_contract.py checks it against mrisim_params_default byte for byte."""
+    import math
+    p = cabi.Params()
+    vals = dict(g=42.5781e6, scale=2.0, border=6.0, num_threads=16, sprintSteps=20000, num_water=4032, num_cells=270,
+                cell_r=.55, mmoment=3.5e-17, kick_mode=cabi.KICK_RANDOM, avoid_intracellular_throw=1,
+                phase_stdev=2 * 3.14 * 1.5 * 1e-3 * 42 * 12 * 10e-3, phase_k=5.0, bound=30.0, water_start_bound=10.0,
+                hashDim=20, maxNeighbors=13, D_cell=.5547, D_extra=1.6642, P_expr=0.2, tau=1e-6, totaltime=40, taucp=5.5,
+                reflectIO=0.0, reflectOI=0.0)
+    vals.update(over)
+    for k, v in vals.items():
+        setattr(p, k, v)
+    p.t = int(p.totaltime / p.tau); p.tcp = int(p.taucp / p.tau); p.pfreq = int(1e-3 / p.tau)       # parameters.h:93,95; cuda_sim.cu:44-45
+    p.in_stdev = math.sqrt(math.pi * p.D_cell * p.tau); p.out_stdev = math.sqrt(math.pi * p.D_extra * p.tau)   # :120-121
+    return p
+
+
+#: workload -> (oracle/_ref binary = the reference's own host scene code compiled in place, its seed)
+REF_SCENES = {"cfg4a_dense2000cells_1Mi_waters_per_gpu": ("ref_scene_dense2000_32k", 11)}
+
+
+def reference_scene(workload):
+    """Scene + waters for the CPU arm from the REFERENCE'S OWN host code (oracle/_ref/ref_scene_*: BacteriaBox,
+    SimulationBox, octree .cpp compiled where they lie), read with the pure-Python MRISCN01 reader.  Returns
+    None when the binary is not there (then the arm falls back to the product's byte-identical builder)."""
+    name = REF_SCENES.get(workload)
+    exe = name and os.path.join(ROOT, "oracle", "_ref", name[0])
+    if not exe or not os.path.exists(exe):
+        return None
+    from mri_nanoparticle_simulation_b200 import scene_io, _cabi as cabi
+    path = f"/tmp/mrisim_refarm_{name[0]}_seed{name[1]}.scn"
+    if not os.path.exists(path):
+        t = time.time()
+        subprocess.run([exe, str(name[1]), path + ".tmp"], check=True, stdout=subprocess.DEVNULL)
+        os.replace(path + ".tmp", path)
+        log(f"[bench] reference scene by {name[0]} (the reference's own host code) in {time.time() - t:.1f} s")
+    sc = scene_io.load(path)
+    over, _, _ = WORKLOADS[workload]
+    p = shipped_params(cabi, **over)
+    assert (sc.num_cells, sc.hash_dim, sc.max_neighbors) == (p.num_cells, p.hashDim, p.maxNeighbors)
+    waters = np.zeros(sc.num_water, dtype=cabi.WATER_DTYPE)
+    for i, k in enumerate(("x", "y", "z", "phase")):
+        waters[k] = sc.waters[:, i]
+    waters["nearest"] = -1
+    return sc, p, waters
+
+
+def run_reference_arm(args, api_loader, ol):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     n_threads = os.cpu_count() or 1
-    box, p, n_per_gpu = get_scene(api, args.workload, 0, 1, lambda: None)
-    waters = throw_waters(box, p, min(n_per_gpu, 1 << 18), 0)
+    ref = reference_scene(args.workload)
+    if ref is not None:
+        sc, p, waters = ref
+        scene_by = "oracle/_ref (the reference's own BacteriaBox/SimulationBox/octree .cpp compiled in place)"
+        make_oracle = lambda: ol.Oracle(sc, p)
+    else:
+        api = api_loader()
+        box, p, n_per_gpu = get_scene(api, args.workload, 0, 1, lambda: None)
+        waters = throw_waters(box, p, min(n_per_gpu, 1 << 18), 0)
+        scene_by = "product host builder (byte-identical to the reference's, tests/test_scene_parity.py); oracle/_ref binary absent"
+        make_oracle = lambda: ol.oracle_for_box(box, p)
     steps = p.sprintSteps
     per_step_budget = max(2.0, min(20.0, 150.0 / max(args.steps + args.warmup, 1)))
-    orc, n, _ = cpu_arm(api, ol, box, p, waters, per_step_budget, n_threads, steps)
+    if os.environ.get("MRISIM_REFARM_BUDGET_S"):                 # tests: a short sample
+        per_step_budget = float(os.environ["MRISIM_REFARM_BUDGET_S"])
+    orc, n, _ = cpu_arm(make_oracle, p, waters, per_step_budget, n_threads, steps)
     w = waters[:n].copy(); rng = orc.seed(n, WALKER_SEED)
     time0 = 0
     for _ in range(args.warmup):
@@ -230,9 +295,10 @@ def run_reference_arm(args, api, ol):
         "impl": "reference", "metric": "walker-steps/sec", "value": value, "unit": "walker-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "sprintSteps": steps, "walkers_in_sample": n,
-                   "note": "reference has no CPU walk (SURVEY.md D1): CPU restatement of its device functions (oracle port) "
-                           "over scene arrays from the reference-identical host builder"},
+        "config": {"workload": args.workload, "sprintSteps": steps, "walkers_in_sample": n, "host_cores": n_threads,
+                   "scene_by": scene_by,
+                   "note": "reference has no CPU walk (SURVEY.md D1): CPU restatement of its device functions (oracle port, "
+                           "bit-equal to the reference's kernels: tests/test_ref_gpu_bitpin.py)"},
         "cpu_baseline": {"value": value, "unit": "walker-steps/s", "cores": n_threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "walker-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -254,17 +320,22 @@ def main():
     ap.add_argument("--path-mode", default="auto", choices=["auto", "fused", "pipeline"],
                     help="fused: one thread per walker for the whole sprint; pipeline: the few-walker path; auto: by walker count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-small-configs", action="store_true", help="skip the few-walker block (cfg1/cfg2) of the default line")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     args = ap.parse_args()
     claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: W < 3 warm-up steps does not meet the timing rules")
 
-    from mri_nanoparticle_simulation_b200 import api
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     if args.impl == "reference":
         import oracle_lib as ol          # the one other place bench.py may execute oracle/
-        return run_reference_arm(args, api, ol)
+
+        def api_loader():                # only if oracle/_ref is absent: the product's host scene builder
+            from mri_nanoparticle_simulation_b200 import api
+            return api
+        return run_reference_arm(args, api_loader, ol)
+    from mri_nanoparticle_simulation_b200 import api
 
     import torch
     import torch.distributed as dist
@@ -280,8 +351,14 @@ def main():
     barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
 
     box, p, n_per_gpu = get_scene(api, args.workload, rank, world, barrier, device=local)
+    strong = args.workload in STRONG
+    first_id = rank * n_per_gpu
+    if strong:                                   # the job's walkers, cut into contiguous rank ranges
+        from mri_nanoparticle_simulation_b200 import dist as shard
+        lo, hi = shard.shard_range(n_per_gpu, rank, world)
+        first_id, n_per_gpu = lo, hi - lo
     if args.walkers_per_gpu:
-        n_per_gpu = args.walkers_per_gpu
+        n_per_gpu = args.walkers_per_gpu; first_id = rank * n_per_gpu
     waters = throw_waters(box, p, n_per_gpu, rank, device=local)
     steps = p.sprintSteps
     n_int = steps // p.pfreq
@@ -289,20 +366,30 @@ def main():
     ctx.set_field_mode(api.FIELD_FAST if args.field_mode == "fast" else api.FIELD_EXACT)
     ctx.set_path_mode({"auto": api.PATH_AUTO, "fused": api.PATH_FUSED, "pipeline": api.PATH_PIPELINE}[args.path_mode])
     ctx.set_scene(box)
-    ctx.set_waters(waters, WALKER_SEED, rank * n_per_gpu)
+    ctx.set_waters(waters, WALKER_SEED, first_id)
+    if world > 1:
+        # the path's one exchange runs inside libmrisim.so: the context owns an NCCL communicator (rank 0's
+        # unique id travels through torch.distributed, which stays the plumbing: barriers, max over ranks)
+        ids = [api.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, device=dev)
+        ctx.comm_init_rank(ids[0], world, rank)
+        if rank == 0:
+            log(f"[bench] NCCL bound by libmrisim.so: {api.nccl_origin()}; communicator of {ctx.comm_size} ranks")
 
-    stream = torch.cuda.Stream(device=dev)       # everything timed runs on this one stream
+    stream = torch.cuda.Stream(device=dev)       # the sprint's kernels run on this stream, the exchange on the context's side stream
     torch.cuda.set_stream(stream)
-    sig = torch.zeros(n_int, dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def one_step():
-        ctx.run_sprint_async(steps, sig.data_ptr(), stream.cuda_stream)
-        if world > 1:
-            dist.all_reduce(sig)            # the path's only exchange: 20 doubles per sprint
+        # mrisim_submit_sprint: kernels on `stream`; on the side stream the all-reduce of the 20 samples (N > 1)
+        # and their D2H.  The step's event pair closes only after that exchange (stream_wait_sprint), so a
+        # step's time includes its own all-reduce (in a production loop it overlaps the next sprint instead).
+        ctx.submit_sprint(steps, stream.cuda_stream)
+        ctx.stream_wait_sprint(stream.cuda_stream)
 
     for _ in range(args.warmup):
         one_step()
+        ctx.wait_sprint(steps)
     torch.cuda.synchronize(); barrier()
 
     fp64_peak = api.measure_fp64_tflops(local)
@@ -318,6 +405,7 @@ def main():
         one_step()
         b.record(stream)
         b.synchronize()
+        signal_last = ctx.wait_sprint(steps)          # the all-reduced samples, already on the host
         kernel_ms.append(ctx.last_sprint_kernel_ms())
     torch.cuda.synchronize(); barrier()
     wall = time.perf_counter() - wall0
@@ -328,21 +416,19 @@ def main():
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_s = float(total_ms.item()) * 1e-3
-    n_total = n_per_gpu * world
+    n_total = WORKLOADS[args.workload][2] if strong and not args.walkers_per_gpu else n_per_gpu * world
     value = n_total * steps * args.steps / total_s
-    signal_last = sig.cpu().numpy().copy()
 
     # ---- e2e: the same sprint through the host-buffer C-ABI calls a user makes ----------
     host_w = ctx.get_waters()
     h2d = host_w.nbytes; d2h = host_w.nbytes + n_int * 8
-    e2e_steps = max(1, min(args.steps, 3))
+    e2e_steps = args.steps
     torch.cuda.synchronize(); barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ctx.set_waters(host_w, WALKER_SEED, rank * n_per_gpu)       # H2D of the walker records (pinned staging)
-        part = ctx.run_sprint(steps)                                 # D2H of the 20 samples
-        if world > 1:
-            t = torch.from_numpy(part).to(dev); dist.all_reduce(t); part = t.cpu().numpy()
+        ctx.set_waters(host_w, WALKER_SEED, first_id)               # H2D of the walker records (pinned staging)
+        ctx.submit_sprint(steps)                                     # kernels + all-reduce (N > 1) + D2H of the 20 samples
+        part = ctx.wait_sprint(steps)
         host_w = ctx.get_waters()                                    # D2H of the walker records
     torch.cuda.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
@@ -359,22 +445,19 @@ def main():
     F = algorithmic_ops(Cbar, Lbar, Rbar)
     k_ms = float(np.mean(kernel_ms))
     achieved = n_per_gpu * steps * F / (k_ms * 1e-3) / 1e12
-    traffic = None                      # DRAM bytes of one walker-kernel launch (ncu --set full capture of the same launch shape)
-    prof = os.path.join(ROOT, "profiles", "instr_mix_r01.json")
-    if os.path.exists(prof) and args.field_mode == "exact" and args.workload == DEFAULT_WORKLOAD and not args.walkers_per_gpu:
-        try:
-            traffic = json.load(open(prof)).get("dram_bytes_per_launch")
-        except Exception:
-            traffic = None
-    # Issue-slot view: on B200 an FP64 warp instruction holds the SMSP issue port for
-    # two cycles, so the binding resource is issue slots = 2 x FP64 + other instructions.  The
-    # instruction mix per warp-step comes from the committed ncu capture of this kernel; the rate
-    # and the clock are measured live.
-    issue = None
-    mixf = os.path.join(ROOT, "profiles", "instr_mix_r01.json")
-    if os.path.exists(mixf) and args.field_mode == "exact" and clocks and clocks.get("sm_mhz") and not ctx.pipeline_sprints:
-        try:
-            mix = json.load(open(mixf))
+    # Instruction mix of the hot kernel from the committed ncu capture -- only if that capture was taken from
+    # THIS kernel source (digest of csrc/mrisim.cu + include/mrisim_math.h, scripts/make_instr_mix.py).
+    traffic, issue = None, None
+    mix = load_instr_mix()
+    fused = not ctx.pipeline_sprints
+    if mix is not None and mix.get("stale"):
+        issue = {"stale": True, "note": "profiles/instr_mix_r02.json was captured from another version of the kernel source; "
+                                        "no issue-slot view for this line (re-run scripts/make_instr_mix.py on an ncu capture of HEAD)"}
+    elif mix is not None and args.field_mode == "exact" and args.workload == DEFAULT_WORKLOAD and not args.walkers_per_gpu and fused:
+        traffic = mix.get("dram_bytes_per_launch")
+        if clocks and clocks.get("sm_mhz"):
+            # Issue-slot view: an FP64 warp instruction holds the SMSP issue port for two cycles on
+            # B200, so the binding resource is issue slots = 2 x FP64 + other instructions; the rate and the clock are live.
             n_sm = torch.cuda.get_device_properties(local).multi_processor_count
             warp_steps_per_s = n_per_gpu / 32.0 * steps / (k_ms * 1e-3)
             cyc_per_s = n_sm * 4 * clocks["sm_mhz"] * 1e6
@@ -382,30 +465,35 @@ def main():
                      "issue_slots_per_warp_step": mix["issue_slots_per_warp_step"],
                      "issue_slot_frac": mix["issue_slots_per_warp_step"] * warp_steps_per_s / cyc_per_s,
                      "fp64_pipe_frac": 2 * mix["fp64_inst_per_warp_step"] * warp_steps_per_s / cyc_per_s,
-                     "instr_mix_from": "profiles/" + str(mix.get("source", "instr_mix_r01.json")) + " (" + str(mix.get("tag")) + ")",
+                     "instr_mix_from": f"profiles/instr_mix_r02.json (ncu capture {mix.get('tag')}, kernel source digest {mix.get('source_digest', '')[:12]} == this tree's)",
                      "note": "issue slots = 2*FP64 + other warp instructions (an FP64 instruction holds the SMSP issue port for 2 cycles, "
-                             "profiles/fp64_issue_probe_r01.txt); frac = slots issued per SMSP cycle at the sampled SM clock"}
-        except Exception as e:      # a stale or missing profile only removes the extra view
-            issue = {"error": str(e)}
+                             "profiles/fp64_issue_probe_r01.txt); frac = slots issued per SMSP cycle at the sampled SM clock. "
+                             "Explains roofline.frac; does not replace it."}
+    F_survey = F - RNG_FP64_OPS_PER_STEP          # SURVEY.md 8(d)'s count: the contract's Gaussian transform excluded
+    props = torch.cuda.get_device_properties(local)
+    sm_max = (clocks or {}).get("sm_max_mhz") or 1965.0
+    peak_theoretical = props.multi_processor_count * 64 * 2 * sm_max * 1e6 / 1e12      # 64 FP64 FMA lanes per SM
     line = {
         "metric": "walker-steps/sec", "value": value, "unit": "walker-steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "walkers_per_gpu": n_per_gpu, "walkers_total": n_total,
                    "sprintSteps": steps, "signal_samples_per_step": n_int, "num_cells": p.num_cells,
                    "octree_nodes": int(len(box.getOctree().nodes)), "field_mode": args.field_mode,
                    "path_mode": args.path_mode, "pipeline_sprints": ctx.pipeline_sprints,
                    "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
-                   "parallelism": f"walker-sharded x{world}, scene replicated, 1 all-reduce of {n_int} f64 per step"},
+                   "parallelism": f"walker-sharded x{world}, scene replicated, 1 ncclAllReduce of {n_int} f64 per step issued by libmrisim.so on a side stream"},
         "e2e": {"value": e2e_value, "unit": "walker-steps/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "steps": e2e_steps, "call": "mrisim_set_waters + mrisim_run_sprint + mrisim_get_waters (host buffers)"},
+                "steps": e2e_steps, "call": "mrisim_set_waters + mrisim_submit_sprint/mrisim_wait_sprint + mrisim_get_waters (host buffers)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
+                     "frac_survey_F": achieved * F_survey / F / fp64_peak, "peak_theoretical": peak_theoretical,
+                     "frac_of_theoretical": achieved / peak_theoretical,
                      "traffic": traffic, "kernel_ms": k_ms,
                      "kernel": "walker_sprint_kernel" if not ctx.pipeline_sprints else
                                "pipelined path (walker_draws + walker_path + step_field + walker_phase kernels; kernel_ms is their sum)",
-                     "algorithmic_fp64_ops_per_walker_step": F, "C_L_R": [Cbar, Lbar, Rbar], "issue": issue,
+                     "algorithmic_fp64_ops_per_walker_step": F, "algorithmic_fp64_ops_survey_8d": F_survey, "C_L_R": [Cbar, Lbar, Rbar], "issue": issue,
                      "peak_source": "measured live: mrisim_measure_fp64_tflops (8 independent DFMA chains/thread, all SMs); "
                                     "MEASURED_PEAKS.json has no FP64 entry",
                      "note": "path is FP64-pipe bound, not HBM/tensor (SURVEY.md 8d): per-step HBM traffic is ~0"},
@@ -415,16 +503,71 @@ def main():
     if not args.no_cpu_baseline and world == 1:
         import oracle_lib as ol          # cpu_baseline leg: the oracle as the thing timed on the host cores
         n_threads = os.cpu_count() or 1
-        orc, n, _ = cpu_arm(api, ol, box, p, waters, args.cpu_budget_s, n_threads, steps)
+        orc, n, _ = cpu_arm(lambda: ol.oracle_for_box(box, p), p, waters, args.cpu_budget_s, n_threads, steps)
         w = waters[:n].copy(); rng = orc.seed(n, WALKER_SEED)
         t = time.perf_counter(); orc.run_sprint(w, rng, 0, steps, n_threads=n_threads); dt = time.perf_counter() - t
         line["cpu_baseline"] = {"value": n * steps / dt, "unit": "walker-steps/s", "cores": n_threads, "kind": "port",
                                 "sample": f"first {n} walkers of rank 0 x {steps} timesteps (one sprint), {dt:.1f} s, "
                                           f"{n_threads} pthreads over walkers"}
+    if world == 1 and args.workload == DEFAULT_WORKLOAD and not args.no_small_configs:
+        ctx.close()
+        line["small_configs"] = small_configs(api, torch, local, args)
     emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def kernel_source_digest():
+    import hashlib
+    h = hashlib.sha256()
+    for rel in ("mri_nanoparticle_simulation_b200/csrc/mrisim.cu", "include/mrisim_math.h"):
+        with open(os.path.join(ROOT, rel), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def load_instr_mix():
+    path = os.path.join(ROOT, "profiles", "instr_mix_r02.json")
+    if not os.path.exists(path):
+        return None
+    try:
+        mix = json.load(open(path))
+    except Exception:
+        return None
+    if mix.get("source_digest") != kernel_source_digest():
+        return {"stale": True}
+    return mix
+
+
+def small_configs(api, torch, local, args, sprints=5, warm=2):
+    """The reference's own shipped sizes (BASELINE configs[0-1]: 4032 / 8000 waters, the few-walker path),
+    device-timed with CUDA events on the launch stream, L2 flushed between sprints: one entry per config."""
+    out = {}
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", local))
+    for name in SMALL_CONFIGS:
+        box, p, n = get_scene(api, name, 0, 1, lambda: None, device=local)
+        waters = throw_waters(box, p, n, 0, device=local)
+        ctx = api.WalkerContext(p, local)
+        ctx.set_scene(box)
+        ctx.set_waters(waters, WALKER_SEED, 0)
+        steps = p.sprintSteps
+        for _ in range(warm):
+            ctx.submit_sprint(steps, stream.cuda_stream); ctx.wait_sprint(steps)
+        ms = []
+        for _ in range(sprints):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            ctx.submit_sprint(steps, stream.cuda_stream); ctx.stream_wait_sprint(stream.cuda_stream)
+            b.record(stream); b.synchronize()
+            ctx.wait_sprint(steps)
+            ms.append(a.elapsed_time(b))
+        out[name] = {"value": n * steps * sprints / (sum(ms) * 1e-3), "unit": "walker-steps/s", "walkers": n, "sprints": sprints,
+                     "ms_per_sprint": sum(ms) / sprints, "path": "pipeline" if ctx.pipeline_sprints else "fused"}
+        ctx.close()
+    return out
 
 
 if __name__ == "__main__":

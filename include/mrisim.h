@@ -251,6 +251,105 @@ int  mrisim_run_sprint(mrisim_ctx* ctx, int32_t steps, double* signal_out);
  * all-reduce).  The caller synchronises that stream before touching walker state. */
 int  mrisim_run_sprint_async(mrisim_ctx* ctx, int32_t steps, double* signal_out_dev, void* cuda_stream);
 void* mrisim_ctx_stream(mrisim_ctx* ctx);     /* the cudaStream_t the synchronous calls use */
+/* Ordering rules of the asynchronous call.  The context records an event on `cuda_stream` at the end of
+ * every sprint; the state accessors (get/set_waters, get/set_rng, get_order, checkpoints) make the
+ * context's own stream wait for it, so state read after an async sprint is never stale.  Two sprints
+ * launched on DIFFERENT streams are not ordered against each other -- that is the caller's job.
+ * mrisim_check() waits for the last sprint launched so far and reads AND clears the device error flag
+ * (a walker that left the lookup lattice, where the reference would read out of bounds, cuda_sim.cu:455-463);
+ * the synchronous calls do that themselves, mrisim_set_waters() starts every walker set with a clear flag. */
+int  mrisim_check(mrisim_ctx* ctx);
+
+/* Submitted sprints -- the sprint loop without a host stall per sprint (the reference blocks on
+ * thrust::reduce 20 times per sprint, cuda_sim.cu:1013).  mrisim_submit_sprint() enqueues the sprint's
+ * kernels on `compute_stream` (NULL: the context's own) and, on a SIDE stream that waits for them, the
+ * in-place SUM all-reduce of the steps/pfreq samples over the attached communicator (if any) and their
+ * copy to pinned host memory -- so the exchange of sprint k overlaps the kernels of sprint k+1.
+ * mrisim_wait_sprint() blocks until the OLDEST outstanding sprint's samples are on the host, copies them
+ * to signal_out (steps/pfreq doubles: the GLOBAL signal when a communicator is attached) and reports the
+ * error flag.  At most four sprints may be outstanding.  mrisim_stream_wait_sprint() makes a caller
+ * stream wait for the most recently submitted sprint's exchange (device-side, for event timing). */
+int  mrisim_submit_sprint(mrisim_ctx* ctx, int32_t steps, void* compute_stream);
+int  mrisim_wait_sprint(mrisim_ctx* ctx, double* signal_out);
+int  mrisim_stream_wait_sprint(mrisim_ctx* ctx, void* cuda_stream);
+int  mrisim_pending_sprints(const mrisim_ctx* ctx);
+
+/* Communicator of the per-sprint signal all-reduce (no reference analogue: the reference drives one
+ * device, `Handler handle(0)`, cuda_sim.cu:916).  NCCL is bound at run time: an NCCL already loaded in
+ * the process (e.g. PyTorch's) is used, else $MRISIM_NCCL_LIB, else the system libnccl.so.2.
+ * One process per GPU: rank 0 calls mrisim_nccl_unique_id(), ships the 128 bytes to the other ranks by
+ * any means, every rank calls mrisim_comm_init_rank() (collective).  One process, several GPUs: see
+ * mrisim_group_* below.  mrisim_comm_attach() borrows an ncclComm_t the caller owns (NULL detaches). */
+int  mrisim_nccl_unique_id(void* id_out_128_bytes);
+int  mrisim_comm_init_rank(mrisim_ctx* ctx, const void* id_128_bytes, int nranks, int rank);
+int  mrisim_comm_attach(mrisim_ctx* ctx, void* nccl_comm, int nranks, int rank);
+int  mrisim_comm_size(const mrisim_ctx* ctx);
+const char* mrisim_nccl_origin(void);         /* which NCCL was bound, and its version (or why none) */
+
+/* walker order of the one-thread-per-walker path (a permutation sorted by octree leaf between launches;
+ * it fixes the association order of the signal sum, nothing per walker).  Saved/restored by checkpoints so
+ * that a resumed run prints byte-identical rows.  valid = 0: the context holds no order yet. */
+int  mrisim_get_order(mrisim_ctx* ctx, uint32_t* perm, uint32_t* keys, uint64_t n, int32_t* valid);
+int  mrisim_set_order(mrisim_ctx* ctx, const uint32_t* perm, const uint32_t* keys, uint64_t n);
+
+/* what the context holds (checkpoint headers, group bookkeeping) */
+uint64_t mrisim_walker_count(const mrisim_ctx* ctx);
+uint64_t mrisim_first_walker_id(const mrisim_ctx* ctx);
+uint64_t mrisim_walker_seed(const mrisim_ctx* ctx);
+uint64_t mrisim_ctx_scene_digest(mrisim_ctx* ctx);       /* FNV-1a of the uploaded scene arrays, 0: incomplete */
+const mrisim_params* mrisim_ctx_params(const mrisim_ctx* ctx);
+int  mrisim_ctx_device(const mrisim_ctx* ctx);
+
+/* -------------------------------------------------------------------------------------
+ * Checkpoint / resume (no reference analogue -- its walker state does round-trip
+ * through d.waters once per sprint, cuda_sim.cu:694,744, which makes a sprint boundary the natural
+ * checkpoint, and the CSV row of :1022 the natural unit of output to resume after).
+ * File "MRICKP01": header (parameter hash, scene digest, host/walker seeds, time, CSV byte offset,
+ * walker range, shard table) + SoA walker state (x y z phase spare s0 s1 nearest in_cell) + per shard
+ * the walker order.  Written to <path>.tmp and renamed.  A file written by a group of k devices can be
+ * loaded by a single context or a group of any size (the walker order is restored where the shard
+ * boundaries coincide, recomputed elsewhere -- it only affects the last bits of the signal sum).
+ * ----------------------------------------------------------------------------------- */
+typedef struct mrisim_checkpoint_info {
+    uint64_t params_hash, scene_digest, host_seed, walker_seed;
+    int64_t  time_steps;
+    uint64_t csv_bytes;
+    uint64_t n_walkers, first_walker_id;
+    uint32_t n_shards, version;
+} mrisim_checkpoint_info;
+uint64_t mrisim_params_hash(const mrisim_params* p);      /* every knob that changes the walk (not num_threads, totaltime, t) */
+int  mrisim_checkpoint_save(mrisim_ctx* ctx, const char* path, uint64_t host_seed, uint64_t csv_bytes);
+int  mrisim_checkpoint_info_read(const char* path, mrisim_checkpoint_info* out);
+/* load walkers [lo, lo + count) of the file into ctx (scene must be set; count = 0: all of them);
+ * refuses a file whose parameter hash or scene digest differs from the context's */
+int  mrisim_checkpoint_load(mrisim_ctx* ctx, const char* path, uint64_t lo, uint64_t count);
+const char* mrisim_checkpoint_last_error(void);
+
+/* -------------------------------------------------------------------------------------
+ * Device group: ONE process driving several GPUs (north-star: walkers shard over the 8 B200s of a
+ * box, scene replicated, one NCCL all-reduce of the signal partials per sprint).  Replaces
+ * `Handler handle(0)` (cuda_sim.cu:916).  The walker array is cut into contiguous ranges (sizes differ
+ * by at most one), walker i keeps the stream of its GLOBAL index, so any device count produces the
+ * same per-walker results as one device.  ncclCommInitAll over the device list; n_devices == 1 needs no NCCL.
+ * ----------------------------------------------------------------------------------- */
+typedef struct mrisim_group mrisim_group;
+int  mrisim_group_create(const mrisim_params* p, const int* devices, int n_devices, mrisim_group** out);
+void mrisim_group_destroy(mrisim_group* g);
+const char* mrisim_group_last_error(const mrisim_group* g);          /* g may be NULL: last create error */
+int  mrisim_group_size(const mrisim_group* g);
+mrisim_ctx* mrisim_group_ctx(mrisim_group* g, int i);                /* member i (field/path mode knobs, accessors) */
+int  mrisim_group_set_scene(mrisim_group* g, const mrisim_scene* s);
+int  mrisim_group_set_waters(mrisim_group* g, const mrisim_water* waters, uint64_t n, uint64_t walker_seed, uint64_t first_walker_id);
+int  mrisim_group_get_waters(mrisim_group* g, mrisim_water* out, uint64_t n);
+int  mrisim_group_get_rng(mrisim_group* g, mrisim_rng_state* out, uint64_t n);
+int64_t mrisim_group_get_time(const mrisim_group* g);
+/* submit on every member (kernels, then ONE grouped all-reduce on the side streams), wait for the oldest */
+int  mrisim_group_submit_sprint(mrisim_group* g, int32_t steps);
+int  mrisim_group_wait_sprint(mrisim_group* g, double* signal_out);
+int  mrisim_group_run_sprint(mrisim_group* g, int32_t steps, double* signal_out);     /* submit + wait */
+int  mrisim_group_checkpoint_save(mrisim_group* g, const char* path, uint64_t host_seed, uint64_t csv_bytes);
+int  mrisim_group_checkpoint_load(mrisim_group* g, const char* path);
+uint64_t mrisim_group_kernel_launches(const mrisim_group* g);
 
 /* Test hook: a sprint that also records, for every (step, walker), position, in_cell and
  * the flat octree leaf index (= subtree_prefix[i] + j of the reference's (i, j)).  Arrays
@@ -279,6 +378,16 @@ int  mrisim_csv_row(int64_t time_steps, double tau, double target, char* buf, si
  * `void simulateWaters(std::string)` (csrc/simulate_waters.cpp) forwards here. */
 int  mrisim_simulate_waters(const char* filename, const mrisim_params* p, uint64_t host_seed,
                             uint64_t walker_seed, int device, int64_t max_sprints);
+/* Same on a list of devices (walkers sharded, one all-reduce per sprint overlapped with the next sprint's
+ * kernels, rank-0 CSV), with checkpoints: every `checkpoint_every` sprints (0: never) the state goes to
+ * `checkpoint_path` (NULL: "<filename>.ckpt"); `resume_path` (NULL: fresh run) continues a run from such
+ * a file -- seeds and time come from the file, the CSV is truncated to the recorded offset and appended
+ * to, and the final CSV is byte-identical to an uninterrupted run's.
+ * Environment of both calls (the drop-in has no other way to take options): MRISIM_DEVICES=0,1,..
+ * overrides the device (list); MRISIM_CHECKPOINT_EVERY, MRISIM_CHECKPOINT, MRISIM_RESUME as above. */
+int  mrisim_simulate_waters_multi(const char* filename, const mrisim_params* p, uint64_t host_seed,
+                                  uint64_t walker_seed, const int* devices, int n_devices, int64_t max_sprints,
+                                  int64_t checkpoint_every, const char* checkpoint_path, const char* resume_path);
 
 /* FP64 pipe micro-benchmark used as the roofline denominator: dependent-free DFMA chains
  * on every SM; returns achieved FP64 FMA TFLOP/s (2 flop per FMA) or <0 on error. */

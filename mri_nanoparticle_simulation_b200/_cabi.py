@@ -51,6 +51,13 @@ class OctreeBuildStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class CheckpointInfo(C.Structure):
+    """``mrisim_checkpoint_info`` (include/mrisim.h)."""
+    _fields_ = [("params_hash", C.c_uint64), ("scene_digest", C.c_uint64), ("host_seed", C.c_uint64), ("walker_seed", C.c_uint64),
+                ("time_steps", C.c_int64), ("csv_bytes", C.c_uint64), ("n_walkers", C.c_uint64), ("first_walker_id", C.c_uint64),
+                ("n_shards", C.c_uint32), ("version", C.c_uint32)]
+
+
 #: ``mrisim_water`` == reference ``water_info`` (src/rand_walk.h:25-53), 40 bytes
 WATER_DTYPE = np.dtype({
     "names": ["x", "y", "z", "phase", "in_cell", "nearest"],

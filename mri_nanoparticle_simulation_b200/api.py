@@ -90,6 +90,46 @@ def lib():
         "mrisim_selftest_sqrt_div": (i64, [C.c_int, dbl, dbl, u64]),
         "mrisim_selftest_index": (i64, [C.c_int, dbl, i32, u64]),
         "mrisim_simulate_waters": (C.c_int, [C.c_char_p, PP, u64, u64, C.c_int, i64]),
+        "mrisim_simulate_waters_multi": (C.c_int, [C.c_char_p, PP, u64, u64, C.POINTER(C.c_int), C.c_int, i64, i64, C.c_char_p, C.c_char_p]),
+        "mrisim_check": (C.c_int, [vp]),
+        "mrisim_submit_sprint": (C.c_int, [vp, i32, vp]),
+        "mrisim_wait_sprint": (C.c_int, [vp, vp]),
+        "mrisim_stream_wait_sprint": (C.c_int, [vp, vp]),
+        "mrisim_pending_sprints": (C.c_int, [vp]),
+        "mrisim_nccl_unique_id": (C.c_int, [vp]),
+        "mrisim_comm_init_rank": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+        "mrisim_comm_attach": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+        "mrisim_comm_size": (C.c_int, [vp]),
+        "mrisim_nccl_origin": (C.c_char_p, []),
+        "mrisim_get_order": (C.c_int, [vp, vp, vp, u64, C.POINTER(i32)]),
+        "mrisim_set_order": (C.c_int, [vp, vp, vp, u64]),
+        "mrisim_walker_count": (u64, [vp]),
+        "mrisim_first_walker_id": (u64, [vp]),
+        "mrisim_walker_seed": (u64, [vp]),
+        "mrisim_ctx_scene_digest": (u64, [vp]),
+        "mrisim_ctx_params": (PP, [vp]),
+        "mrisim_ctx_device": (C.c_int, [vp]),
+        "mrisim_params_hash": (u64, [PP]),
+        "mrisim_checkpoint_save": (C.c_int, [vp, C.c_char_p, u64, u64]),
+        "mrisim_checkpoint_info_read": (C.c_int, [C.c_char_p, C.POINTER(cabi.CheckpointInfo)]),
+        "mrisim_checkpoint_load": (C.c_int, [vp, C.c_char_p, u64, u64]),
+        "mrisim_checkpoint_last_error": (C.c_char_p, []),
+        "mrisim_group_create": (C.c_int, [PP, C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]),
+        "mrisim_group_destroy": (None, [vp]),
+        "mrisim_group_last_error": (C.c_char_p, [vp]),
+        "mrisim_group_size": (C.c_int, [vp]),
+        "mrisim_group_ctx": (vp, [vp, C.c_int]),
+        "mrisim_group_set_scene": (C.c_int, [vp, vp]),
+        "mrisim_group_set_waters": (C.c_int, [vp, vp, u64, u64, u64]),
+        "mrisim_group_get_waters": (C.c_int, [vp, vp, u64]),
+        "mrisim_group_get_rng": (C.c_int, [vp, vp, u64]),
+        "mrisim_group_get_time": (i64, [vp]),
+        "mrisim_group_submit_sprint": (C.c_int, [vp, i32]),
+        "mrisim_group_wait_sprint": (C.c_int, [vp, vp]),
+        "mrisim_group_run_sprint": (C.c_int, [vp, i32, vp]),
+        "mrisim_group_checkpoint_save": (C.c_int, [vp, C.c_char_p, u64, u64]),
+        "mrisim_group_checkpoint_load": (C.c_int, [vp, C.c_char_p]),
+        "mrisim_group_kernel_launches": (u64, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError here = the ABI and the header disagree
@@ -110,6 +150,15 @@ ABI_SYMBOLS = [
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_trace_sprint_kicks", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
     "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index",
+    "mrisim_simulate_waters_multi", "mrisim_check", "mrisim_submit_sprint", "mrisim_wait_sprint", "mrisim_stream_wait_sprint", "mrisim_pending_sprints",
+    "mrisim_nccl_unique_id", "mrisim_comm_init_rank", "mrisim_comm_attach", "mrisim_comm_size", "mrisim_nccl_origin",
+    "mrisim_get_order", "mrisim_set_order", "mrisim_walker_count", "mrisim_first_walker_id", "mrisim_walker_seed",
+    "mrisim_ctx_scene_digest", "mrisim_ctx_params", "mrisim_ctx_device", "mrisim_params_hash",
+    "mrisim_checkpoint_save", "mrisim_checkpoint_info_read", "mrisim_checkpoint_load", "mrisim_checkpoint_last_error",
+    "mrisim_group_create", "mrisim_group_destroy", "mrisim_group_last_error", "mrisim_group_size", "mrisim_group_ctx",
+    "mrisim_group_set_scene", "mrisim_group_set_waters", "mrisim_group_get_waters", "mrisim_group_get_rng", "mrisim_group_get_time",
+    "mrisim_group_submit_sprint", "mrisim_group_wait_sprint", "mrisim_group_run_sprint",
+    "mrisim_group_checkpoint_save", "mrisim_group_checkpoint_load", "mrisim_group_kernel_launches",
 ]
 
 
@@ -255,9 +304,14 @@ class BacteriaBox:
 class WalkerContext:
     """Device context of the sprint loop (src/cuda_sim.cu:923-1024 minus the CSV line)."""
 
-    def __init__(self, params: Params, device: int = 0):
+    def __init__(self, params: Params, device: int = 0, _borrowed=None):
         self.params = params.copy()
         self._h = C.c_void_p()
+        self._owned = _borrowed is None
+        if _borrowed is not None:                      # a member of a WalkerGroup: the group owns the handle
+            self._h = C.c_void_p(_borrowed)
+            self.n = int(lib().mrisim_walker_count(self._h))
+            return
         if lib().mrisim_create(C.byref(self.params), device, C.byref(self._h)):
             raise MrisimError(lib().mrisim_last_error(None).decode())
         self.n = 0
@@ -359,6 +413,59 @@ class WalkerContext:
                                                  tr["kick"].ctypes.data if kicks else None))
         return sig, tr
 
+    # ---- submitted sprints, communicator, checkpoints (include/mrisim.h) ---------------------------
+    def check(self):
+        """Wait for the last sprint launched so far; read and clear the device error flag."""
+        self._ck(lib().mrisim_check(self._h))
+
+    def submit_sprint(self, steps: Optional[int] = None, stream: int = 0):
+        """Enqueue a sprint (kernels on ``stream`` or the context's own; all-reduce over the attached
+        communicator and D2H of the samples on the side stream) and return at once."""
+        steps = self.params.sprintSteps if steps is None else steps
+        self._ck(lib().mrisim_submit_sprint(self._h, steps, stream or None))
+
+    def wait_sprint(self, steps: Optional[int] = None) -> np.ndarray:
+        """Samples of the oldest outstanding sprint (global signal when a communicator is attached)."""
+        steps = self.params.sprintSteps if steps is None else steps
+        out = np.zeros(max(steps // max(self.params.pfreq, 1), 1), dtype=np.float64)
+        self._ck(lib().mrisim_wait_sprint(self._h, out.ctypes.data))
+        return out
+
+    def stream_wait_sprint(self, stream: int):
+        self._ck(lib().mrisim_stream_wait_sprint(self._h, stream))
+
+    @property
+    def pending_sprints(self) -> int:
+        return int(lib().mrisim_pending_sprints(self._h))
+
+    def comm_init_rank(self, unique_id: bytes, nranks: int, rank: int):
+        """Collective: every rank passes the 128 bytes rank 0 got from ``nccl_unique_id()``."""
+        assert len(unique_id) == 128
+        buf = C.create_string_buffer(unique_id, 128)
+        self._ck(lib().mrisim_comm_init_rank(self._h, buf, nranks, rank))
+
+    @property
+    def comm_size(self) -> int:
+        return int(lib().mrisim_comm_size(self._h))
+
+    def get_order(self):
+        perm = np.zeros(self.n, np.uint32); keys = np.zeros(self.n, np.uint32); valid = C.c_int32()
+        self._ck(lib().mrisim_get_order(self._h, perm.ctypes.data, keys.ctypes.data, self.n, C.byref(valid)))
+        return (perm, keys) if valid.value else None
+
+    def set_order(self, perm: np.ndarray, keys: np.ndarray):
+        pm = np.ascontiguousarray(perm, np.uint32); ky = np.ascontiguousarray(keys, np.uint32)
+        self._ck(lib().mrisim_set_order(self._h, pm.ctypes.data, ky.ctypes.data, len(pm)))
+
+    def checkpoint_save(self, path: str, host_seed: int = 0, csv_bytes: int = 0):
+        if lib().mrisim_checkpoint_save(self._h, path.encode(), host_seed, csv_bytes):
+            raise MrisimError(lib().mrisim_checkpoint_last_error().decode())
+
+    def checkpoint_load(self, path: str, lo: int = 0, count: int = 0):
+        if lib().mrisim_checkpoint_load(self._h, path.encode(), lo, count):
+            raise MrisimError(lib().mrisim_checkpoint_last_error().decode())
+        self.n = int(lib().mrisim_walker_count(self._h))
+
     @property
     def kernel_launches(self) -> int:
         return lib().mrisim_kernel_launches(self._h)
@@ -367,8 +474,95 @@ class WalkerContext:
         return lib().mrisim_last_sprint_kernel_ms(self._h)
 
     def close(self):
-        if self._h and _lib is not None:
+        if self._h and _lib is not None and self._owned:
             _lib.mrisim_destroy(self._h)
+        self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class WalkerGroup:
+    """One process, several GPUs: walkers sharded over ``devices``, scene replicated, one NCCL
+    all-reduce of the signal partials per sprint on a side stream (``mrisim_group_*``; replaces the
+    reference's ``Handler handle(0)``, src/cuda_sim.cu:916)."""
+
+    def __init__(self, params: Params, devices):
+        self.params = params.copy()
+        self.devices = [int(d) for d in devices]
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        if lib().mrisim_group_create(C.byref(self.params), arr, len(self.devices), C.byref(self._h)):
+            raise MrisimError(lib().mrisim_group_last_error(None).decode())
+        self.n = 0
+
+    def _ck(self, rc):
+        if rc:
+            raise MrisimError(lib().mrisim_group_last_error(self._h).decode())
+
+    def member(self, i: int) -> WalkerContext:
+        h = lib().mrisim_group_ctx(self._h, i)
+        if not h:
+            raise IndexError(i)
+        return WalkerContext(self.params, _borrowed=h)
+
+    def __len__(self):
+        return int(lib().mrisim_group_size(self._h))
+
+    def set_scene(self, box: BacteriaBox):
+        self._ck(lib().mrisim_group_set_scene(self._h, box._handle()))
+
+    def set_waters(self, waters: np.ndarray, walker_seed: int, first_walker_id: int = 0):
+        w = np.ascontiguousarray(waters)
+        assert w.dtype == cabi.WATER_DTYPE
+        self._ck(lib().mrisim_group_set_waters(self._h, w.ctypes.data, len(w), walker_seed, first_walker_id))
+        self.n = len(w)
+
+    def get_waters(self) -> np.ndarray:
+        out = np.zeros(self.n, dtype=cabi.WATER_DTYPE)
+        self._ck(lib().mrisim_group_get_waters(self._h, out.ctypes.data, self.n))
+        return out
+
+    def get_rng(self) -> np.ndarray:
+        out = np.zeros(self.n, dtype=cabi.RNG_DTYPE)
+        self._ck(lib().mrisim_group_get_rng(self._h, out.ctypes.data, self.n))
+        return out
+
+    @property
+    def time(self) -> int:
+        return lib().mrisim_group_get_time(self._h)
+
+    def submit_sprint(self, steps: Optional[int] = None):
+        self._ck(lib().mrisim_group_submit_sprint(self._h, self.params.sprintSteps if steps is None else steps))
+
+    def wait_sprint(self, steps: Optional[int] = None) -> np.ndarray:
+        steps = self.params.sprintSteps if steps is None else steps
+        out = np.zeros(max(steps // max(self.params.pfreq, 1), 1), dtype=np.float64)
+        self._ck(lib().mrisim_group_wait_sprint(self._h, out.ctypes.data))
+        return out
+
+    def run_sprint(self, steps: Optional[int] = None) -> np.ndarray:
+        self.submit_sprint(steps)
+        return self.wait_sprint(steps)
+
+    def checkpoint_save(self, path: str, host_seed: int = 0, csv_bytes: int = 0):
+        self._ck(lib().mrisim_group_checkpoint_save(self._h, path.encode(), host_seed, csv_bytes))
+
+    def checkpoint_load(self, path: str):
+        self._ck(lib().mrisim_group_checkpoint_load(self._h, path.encode()))
+        info = checkpoint_info(path)
+        self.n = int(info.n_walkers)
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(lib().mrisim_group_kernel_launches(self._h))
+
+    def close(self):
+        if self._h and _lib is not None:
+            _lib.mrisim_group_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
@@ -376,6 +570,28 @@ class WalkerContext:
             self.close()
         except Exception:
             pass
+
+
+def nccl_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    if lib().mrisim_nccl_unique_id(buf):
+        raise MrisimError(lib().mrisim_last_error(None).decode())
+    return buf.raw
+
+
+def nccl_origin() -> str:
+    return lib().mrisim_nccl_origin().decode()
+
+
+def checkpoint_info(path: str) -> "cabi.CheckpointInfo":
+    info = cabi.CheckpointInfo()
+    if lib().mrisim_checkpoint_info_read(path.encode(), C.byref(info)):
+        raise MrisimError(lib().mrisim_checkpoint_last_error().decode())
+    return info
+
+
+def params_hash(p: Params) -> int:
+    return int(lib().mrisim_params_hash(C.byref(p)))
 
 
 def csv_row(time_steps: int, tau: float, target: float) -> str:
@@ -395,9 +611,19 @@ def measure_fp64_tflops(device: int = 0, iters: int = 1 << 16) -> float:
 
 
 def simulateWaters(filename: str, params: Optional[Params] = None, host_seed: int = 12345,
-                   walker_seed: int = 0xC0FFEE, device: int = 0, max_sprints: int = -1) -> None:
+                   walker_seed: int = 0xC0FFEE, device: int = 0, max_sprints: int = -1, devices=None,
+                   checkpoint_every: int = 0, checkpoint_path: Optional[str] = None, resume: Optional[str] = None) -> None:
     """``simulateWaters(fName)`` (src/cuda_sim.cu:902-1034) through the C++ drop-in: builds the
-    scene, runs t/sprintSteps sprints on ``device`` and writes the signal CSV to ``filename``."""
+    scene, runs t/sprintSteps sprints on ``device`` (or sharded over ``devices``) and writes the signal
+    CSV to ``filename``; optional on-disk checkpoints every ``checkpoint_every`` sprints and ``resume``."""
     p = params if params is not None else ParameterStruct()
-    if lib().mrisim_simulate_waters(filename.encode(), C.byref(p), host_seed, walker_seed, device, max_sprints):
-        raise MrisimError("simulateWaters failed: " + lib().mrisim_last_error(None).decode())
+    if devices is None and not checkpoint_every and not resume:
+        rc = lib().mrisim_simulate_waters(filename.encode(), C.byref(p), host_seed, walker_seed, device, max_sprints)
+    else:
+        devs = [int(d) for d in (devices if devices is not None else [device])]
+        arr = (C.c_int * len(devs))(*devs)
+        rc = lib().mrisim_simulate_waters_multi(filename.encode(), C.byref(p), host_seed, walker_seed, arr, len(devs), max_sprints,
+                                                checkpoint_every, checkpoint_path.encode() if checkpoint_path else None,
+                                                resume.encode() if resume else None)
+    if rc:
+        raise MrisimError("simulateWaters failed (see stderr)")

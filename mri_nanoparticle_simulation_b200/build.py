@@ -27,10 +27,11 @@ EXE = os.path.join(PKG, "gpu_sim.out")
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
               "-fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", INC] + \
              [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK") if os.environ.get(k)]
-CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC]
+CUDA_INC = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")      # group.cpp: cuda_runtime.h for <nccl.h>
+CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC, "-I", CUDA_INC]
 
 CU_SOURCES = ["mrisim.cu", "octree_build.cu", "scene_gpu.cu"]
-CXX_SOURCES = ["scene.cpp", "simulate_waters.cpp"]
+CXX_SOURCES = ["scene.cpp", "simulate_waters.cpp", "checkpoint.cpp", "group.cpp"]
 
 
 def _nvcc() -> str:
@@ -76,7 +77,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(OBJ, f + ".o")
         _run(["g++"] + CXX_FLAGS + ["-c", src, "-o", o], verbose)
         objs.append(o)
-    _run([_nvcc(), "-shared", "-o", LIB] + objs + ["-Xlinker", "--no-undefined", "-lpthread"], verbose)
+    _run([_nvcc(), "-shared", "-o", LIB] + objs + ["-Xlinker", "--no-undefined", "-lpthread", "-ldl"], verbose)
     main_src = os.path.join(CSRC, "T2_sim_main.cpp")
     if os.path.exists(main_src):
         _run(["g++"] + CXX_FLAGS + ["-I", CSRC, main_src, "-o", EXE, "-L", PKG, "-lmrisim", "-Wl,-rpath,$ORIGIN"], verbose)
