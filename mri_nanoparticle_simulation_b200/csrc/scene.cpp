@@ -722,13 +722,32 @@ int mrisim_scene_save(const mrisim_scene* s, const char* path) {
 }
 
 int mrisim_scene_load(const char* path, mrisim_scene** out) {
+    if (!path || !out) { g_scene_error = "mrisim_scene_load: null argument"; return 1; }
     FILE* f = std::fopen(path, "rb");
     if (!f) { g_scene_error = std::string("mrisim_scene_load: cannot open ") + path; return 1; }
-    std::unique_ptr<mrisim_scene> s(new mrisim_scene);
+    struct Closer { FILE* f; ~Closer() { std::fclose(f); } } closer{f};
+    auto bad = [&](const char* why) { g_scene_error = std::string("mrisim_scene_load: malformed scene file ") + path + " (" + why + ")"; return 1; };
     FileHeader h;
-    bool ok = std::fread(&h, sizeof h, 1, f) == 1 && std::memcmp(h.magic, "MRISCN01", 8) == 0;
-    auto get = [&](void* d, size_t bytes) { if (bytes) ok = ok && std::fread(d, 1, bytes, f) == bytes; };
-    if (ok) {
+    if (std::fread(&h, sizeof h, 1, f) != 1 || std::memcmp(h.magic, "MRISCN01", 8) != 0) return bad("not an MRISCN01 header");
+    // Nothing in the header is trusted: every count is checked for sign and for the bounds the rest of the
+    // library assumes, and the payload size they imply must equal the file's before anything is allocated.
+    if (h.num_cells < 0 || h.num_mnps < 0 || h.num_water < 0 || h.maxNeighbors <= 0 || h.maxNeighbors > 255 ||
+        h.hashDim <= 0 || h.hashDim > 1290 || h.min_depth < 0 || h.min_depth > 8 || h.max_depth < h.min_depth || h.max_depth > 20 ||
+        h.n_subtrees != (1 << (3 * h.min_depth)) || h.n_nodes >= (1ull << 31) || h.n_res >= (1ull << 32) ||
+        !(h.bound > 0.0) || !(h.cell_r > 0.0))
+        return bad("header field out of range");
+    const uint64_t h3 = (uint64_t)h.hashDim * h.hashDim * h.hashDim;
+    const uint64_t payload = (uint64_t)h.num_cells * 3 * sizeof(double) + (uint64_t)h.num_mnps * sizeof(mrisim_mnp) +
+                             h3 * (uint64_t)h.maxNeighbors * sizeof(int32_t) + (uint64_t)h.n_subtrees * sizeof(uint32_t) +
+                             h.n_nodes * sizeof(mrisim_node) + h.n_res * sizeof(mrisim_mnp) + (uint64_t)h.num_water * 4 * sizeof(double);
+    if (std::fseek(f, 0, SEEK_END) != 0) return bad("cannot seek");
+    const long size = std::ftell(f);
+    if (size < 0 || (uint64_t)size != sizeof h + payload) return bad("file size does not match the header");
+    if (std::fseek(f, (long)sizeof h, SEEK_SET) != 0) return bad("cannot seek");
+    try {
+        std::unique_ptr<mrisim_scene> s(new mrisim_scene);
+        bool ok = true;
+        auto get = [&](void* d, size_t bytes) { if (bytes) ok = ok && std::fread(d, 1, bytes, f) == bytes; };
         mrisim_params_default(&s->p);
         s->seed = h.seed;
         s->p.num_cells = h.num_cells; s->p.hashDim = h.hashDim; s->p.maxNeighbors = h.maxNeighbors;
@@ -737,7 +756,7 @@ int mrisim_scene_load(const char* path, mrisim_scene** out) {
         s->min_depth = h.min_depth; s->max_depth = h.max_depth;
         s->cells.resize((size_t)h.num_cells * 3); get(s->cells.data(), s->cells.size() * sizeof(double));
         s->mnps.resize((size_t)h.num_mnps); get(s->mnps.data(), s->mnps.size() * sizeof(mrisim_mnp));
-        s->lookup.resize((size_t)h.hashDim * h.hashDim * h.hashDim * h.maxNeighbors); get(s->lookup.data(), s->lookup.size() * sizeof(int32_t));
+        s->lookup.resize((size_t)(h3 * (uint64_t)h.maxNeighbors)); get(s->lookup.data(), s->lookup.size() * sizeof(int32_t));
         s->subtree_sizes.resize((size_t)h.n_subtrees); get(s->subtree_sizes.data(), s->subtree_sizes.size() * sizeof(uint32_t));
         s->nodes.resize(h.n_nodes); get(s->nodes.data(), s->nodes.size() * sizeof(mrisim_node));
         s->residents.resize(h.n_res); get(s->residents.data(), s->residents.size() * sizeof(mrisim_mnp));
@@ -746,13 +765,23 @@ int mrisim_scene_load(const char* path, mrisim_scene** out) {
             double v[4]; get(v, sizeof v);
             std::memset(&w, 0, sizeof w); w.x = v[0]; w.y = v[1]; w.z = v[2]; w.phase = v[3]; w.nearest = -1;
         }
+        if (!ok) return bad("short read");
         s->prefix.assign(s->subtree_sizes.size() + 1, 0);
         for (size_t i = 0; i < s->subtree_sizes.size(); i++) s->prefix[i + 1] = s->prefix[i] + s->subtree_sizes[i];
-        ok = ok && s->prefix.back() == s->nodes.size();
+        if (s->prefix.back() != s->nodes.size()) return bad("subtree sizes do not cover the node array");
+        // node links: resident ranges inside the residents array, child offsets inside their subtree
+        for (size_t t = 0; t < s->subtree_sizes.size(); t++)
+            for (uint64_t j = s->prefix[t]; j < s->prefix[t + 1]; j++) {
+                const mrisim_node& nd = s->nodes[j];
+                if (nd.mc >> 63) { if ((uint64_t)nd.res_start + nd.n_res > h.n_res) return bad("resident range out of bounds"); }
+                else for (int c = 0; c < 8; c++) if (nd.child[c] == 0 || j + nd.child[c] >= s->prefix[t + 1]) return bad("child offset leaves its subtree");
+            }
+        for (int32_t v : s->lookup) if (v < -1 || v >= h.num_cells) return bad("lookup table names a cell outside the cells set");
+        *out = s.release();
+    } catch (const std::exception& e) {                      // bad_alloc and friends must not cross the C boundary
+        g_scene_error = std::string("mrisim_scene_load: ") + e.what();
+        return 1;
     }
-    std::fclose(f);
-    if (!ok) { g_scene_error = std::string("mrisim_scene_load: malformed scene file ") + path; return 1; }
-    *out = s.release();
     return 0;
 }
 

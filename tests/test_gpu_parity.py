@@ -259,6 +259,45 @@ def test_dense_scene_cfg4a_subsample():
     assert_state_equal(got[sel], sub)
 
 
+def test_dense_scene_cfg4b_subsample():
+    """SURVEY.md 8d config 4b (BASELINE configs[3], octree-heavy): 8000 cells, 21 385 dipoles, 455 008 octree
+    nodes, leaves with up to 104 residents, lookup rows with up to 15 candidates -- the reference loops stressed
+    hardest are get_field's resident loop (cuda_sim.cu:280-283) and updateNearest's scan (:470-481).  The scene is
+    built on the GPU (its digests equal the reference's own host code's, tests/test_octree_gpu.py); 64k walkers
+    thrown anywhere (so that some sit inside cells) run on the GPU, 1024 of them against the oracle -- final
+    state bit-exact -- and a traced sprint of 512 walkers per (step, walker) incl. leaf indices and kicks."""
+    p = api.ParameterStruct(avoid_intracellular_throw=0, **KATS["configs"]["dense8000"])
+    box = api.BacteriaBox(p, 11).populateSimulation(device=0)
+    orc = ol.oracle_for_box(box, p)
+    nodes = box.getOctree().nodes
+    leaf = (nodes["mc"] >> np.uint64(63)) != 0
+    assert len(nodes) == 455008 and int(nodes["n_res"][leaf].max()) == 104
+    assert int((box.getLookupTable() != -1).sum(axis=1).max()) >= 15
+    box.rethrow_waters(65536, 7000, True, p, device=0)
+    w0 = box.getWaters().copy()
+    ctx = gpu_ctx(p, box, w0)
+    ctx.run_sprint(2000)
+    got = ctx.get_waters()
+    sel = np.arange(0, 65536, 64)
+    sub = w0[sel].copy()
+    rng = np.concatenate([orc.seed(1, SEED, int(i)) for i in sel])
+    orc.run_sprint(sub, rng, 0, 2000)
+    assert_state_equal(got[sel], sub)
+    assert int(got["in_cell"].sum()) > 1000, "walkers thrown anywhere in a box that is 6 % cells"
+    # per-step trace of a contiguous block (walkers 4096..4607 keep their global stream ids)
+    first, cnt = 4096, 512
+    tctx = gpu_ctx(p, box, w0[first:first + cnt], first=first)
+    _, tr = tctx.trace_sprint(1000, kicks=True)
+    want, wrng = w0[first:first + cnt].copy(), orc.seed(cnt, SEED, first)
+    _, otr = orc.run_sprint(want, wrng, 0, 1000, trace=True, trace_kick=True)
+    for k in ("x", "y", "z", "in_cell", "leaf"):
+        assert np.array_equal(tr[k], otr[k]), f"cfg4b: per-step {k} differs"
+    assert tr["kick"].tobytes() == otr["kick"].tobytes(), "cfg4b: per-step phase kick differs"
+    n_res_at = nodes["n_res"][otr["leaf"]]
+    print(f"\ncfg4b: residents per step along the traced walk: mean {n_res_at.mean():.2f}, max {int(n_res_at.max())}; "
+          f"in-cell share {tr['in_cell'].mean():.3f}")
+
+
 def test_multi_sprint_with_cpmg_flip_and_resume():
     """Sprints chain through device-resident state; flips land after sampling; a checkpoint
     (waters + rng + time) restored into a fresh context continues bit-identically."""

@@ -100,3 +100,45 @@ def test_rethrow_waters_semantics():
     orc = ol.oracle_for_box(box, p)
     mcs = [orc.probe_leaf(*q)[1] for q in zip(w["x"], w["y"], w["z"])]
     assert mcs == sorted(mcs)
+
+
+def test_scene_load_refuses_malformed_files(tmp_path):
+    """mrisim_scene_load trusts nothing in the header: counts are checked for sign and bounds and the implied
+    payload size must equal the file's before anything is allocated; node links and lookup entries are checked."""
+    import struct
+    p = api.ParameterStruct(num_water=256, num_cells=40, bound=10, water_start_bound=6, hashDim=8, border=3)
+    good = str(tmp_path / "good.scn")
+    api.BacteriaBox(p, 3).populateSimulation().save(good)
+    raw = bytearray(open(good, "rb").read())
+    api.BacteriaBox.load(good, p)                                  # sanity: the untouched file loads
+    hdr = struct.Struct("<8sQ8iQQ4dq")
+    fields = list(hdr.unpack_from(raw, 0))
+
+    def variant(name, **kw):
+        f = list(fields)
+        idx = dict(num_cells=2, num_mnps=3, hashDim=4, maxNeighbors=5, min_depth=6, max_depth=7, num_water=8, n_subtrees=9, n_nodes=10, n_res=11)
+        for k, v in kw.items():
+            f[idx[k]] = v
+        out = bytearray(raw)
+        hdr.pack_into(out, 0, *f)
+        path = str(tmp_path / (name + ".scn"))
+        open(path, "wb").write(out)
+        return path
+
+    for name, kw in [("neg_cells", dict(num_cells=-5)), ("huge_hash", dict(hashDim=2000)), ("huge_nodes", dict(n_nodes=1 << 40)),
+                     ("bad_depth", dict(min_depth=9)), ("bad_subtrees", dict(n_subtrees=7)), ("more_water", dict(num_water=fields[8] + 1)),
+                     ("neg_water", dict(num_water=-1))]:
+        with pytest.raises(api.MrisimError, match="malformed scene file"):
+            api.BacteriaBox.load(variant(name, **kw), p)
+    trunc = str(tmp_path / "trunc.scn")
+    open(trunc, "wb").write(raw[:-8])
+    with pytest.raises(api.MrisimError, match="file size"):
+        api.BacteriaBox.load(trunc, p)
+    # a lookup entry naming a cell that does not exist
+    off = hdr.size + fields[2] * 24 + fields[3] * 40
+    broken = bytearray(raw)
+    struct.pack_into("<i", broken, off, fields[2] + 3)
+    path = str(tmp_path / "lookup.scn")
+    open(path, "wb").write(broken)
+    with pytest.raises(api.MrisimError, match="lookup table"):
+        api.BacteriaBox.load(path, p)
