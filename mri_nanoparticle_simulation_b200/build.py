@@ -26,7 +26,8 @@ EXE = os.path.join(PKG, "gpu_sim.out")
 # octree indices bit-identical to the oracle (see include/mrisim_math.h)
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
               "-fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", INC] + \
-             [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK") if os.environ.get(k)]
+             [f"-D{k}={os.environ[k]}" for k in ("MRISIM_MIN_BLOCKS", "MRISIM_BLOCK") if os.environ.get(k)] + \
+             os.environ.get("MRISIM_DEFS", "").split()            # tuning builds: extra -D switches of csrc/mrisim.cu
 CUDA_INC = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")      # group.cpp: cuda_runtime.h for <nccl.h>
 CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-pthread", "-Wall", "-Wextra", "-I", INC, "-I", CUDA_INC]
 
@@ -62,7 +63,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
               [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h")]
     sources = [os.path.join(CSRC, f) for f in CU_SOURCES + CXX_SOURCES if os.path.exists(os.path.join(CSRC, f))]
     stamp = os.path.join(OBJ, "stamp")
-    dig = _digest(headers + sources, " ".join(NVCC_FLAGS + CXX_FLAGS))
+    # flags enter the digest with the checkout's path taken out: the tree is built here and RUN from another
+    # directory on the GPU box, where a path-dependent digest would trigger a pointless one-minute rebuild
+    dig = _digest(headers + sources, " ".join(NVCC_FLAGS + CXX_FLAGS).replace(ROOT, "."))
     if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == dig:
         return LIB
     objs = []

