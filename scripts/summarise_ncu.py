@@ -3,6 +3,10 @@
 import csv, io, json, os, subprocess, sys
 rep, tag, warp_steps, what = sys.argv[1], sys.argv[2], float(sys.argv[3]), sys.argv[4]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROUND = os.environ.get("ROUND", "r02")                      # file-name prefix under profiles/
+WRITE_MIX = os.environ.get("INSTR_MIX", "1") == "1"         # only the default bench workload's capture feeds bench.py
+sys.path.insert(0, ROOT)
+import bench                                                 # kernel_source_digest(): ties the mix to the kernel source it was captured from
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 h, u = rows[0], rows[1]
@@ -37,12 +41,13 @@ for v in rows[2:]:
         def mb(k):
             v, unit = m[k]
             return float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
-        json.dump({"source": os.path.basename(rep), "tag": tag, "what": what,
-                   "dram_bytes_per_launch": mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), **m["issue_model"]},
-                  open(os.path.join(ROOT, "profiles", "instr_mix_r01.json"), "w"), indent=1)
+        if WRITE_MIX:
+            json.dump({"source": os.path.basename(rep), "tag": tag, "what": what, "source_digest": bench.kernel_source_digest(),
+                       "dram_bytes_per_launch": mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), **m["issue_model"]},
+                      open(os.path.join(ROOT, "profiles", f"instr_mix_{ROUND}.json"), "w"), indent=1)
     out["launches"].append(m)
-json.dump(out, open(os.path.join(ROOT, "profiles", f"ncu_r01_{tag}_summary.json"), "w"), indent=1)
+json.dump(out, open(os.path.join(ROOT, "profiles", f"ncu_{ROUND}_{tag}_summary.json"), "w"), indent=1)
 lines = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "ncu_lines.py"), rep, str(warp_steps), "70"],
                        capture_output=True, text=True).stdout
-open(os.path.join(ROOT, "profiles", f"ncu_r01_{tag}_source_lines.txt"), "w").write(what + "\n" + lines)
+open(os.path.join(ROOT, "profiles", f"ncu_{ROUND}_{tag}_source_lines.txt"), "w").write(what + "\n" + lines)
 print(json.dumps(out["launches"][0], indent=1)[:1500])
