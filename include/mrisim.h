@@ -213,6 +213,13 @@ int  mrisim_set_resort_steps(mrisim_ctx* ctx, int32_t steps);
  * streams, so that the tail of one range's kernel overlaps the body of another's (default 1 = a
  * single chain; 2 and 4 measured no faster on B200).  Per-walker results do not depend on it. */
 int  mrisim_set_overlap_groups(mrisim_ctx* ctx, int32_t groups);
+/* Tasks inside a launch (no reference analogue).  A launch of the fused kernel is cut into tasks of `steps`
+ * timesteps per tile of 128 walkers; CTAs draw tasks from a counter in dispatch order (every tile's first task,
+ * then every tile's second, ...) and hand the tile's state on through global memory, so that the end of a
+ * launch is a tail of short tasks instead of whole-launch CTAs.  Per-walker results and the signal's bits do
+ * not depend on it.  steps < 0: default (on for walker counts that fill the GPU several times over);
+ * steps == 0: off; steps > 0: as given, whatever the walker count. */
+int  mrisim_set_task_steps(mrisim_ctx* ctx, int32_t steps);
 
 /* `p_array<Triple> dev_lattice(p.num_cells, simBox.getCells(), d.lattice)` (cuda_sim.cu:935,960) */
 int  mrisim_set_cells(mrisim_ctx* ctx, const double* xyz, int32_t num_cells);

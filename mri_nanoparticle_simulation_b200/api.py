@@ -67,6 +67,7 @@ def lib():
         "mrisim_pipeline_sprints": (C.c_uint64, [vp]),
         "mrisim_set_resort_steps": (C.c_int, [vp, i32]),
         "mrisim_set_overlap_groups": (C.c_int, [vp, i32]),
+        "mrisim_set_task_steps": (C.c_int, [vp, i32]),
         "mrisim_set_cells": (C.c_int, [vp, vp, i32]),
         "mrisim_set_lookup": (C.c_int, [vp, vp, i32, i32]),
         "mrisim_set_octree": (C.c_int, [vp, i32, i32, vp, i32, vp, u64, vp, u64]),
@@ -144,7 +145,7 @@ ABI_SYMBOLS = [
     "mrisim_scene_build", "mrisim_scene_build_gpu", "mrisim_octree_build_set_margin_scale", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters", "mrisim_scene_rethrow_waters_gpu",
-    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
+    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups", "mrisim_set_task_steps",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
@@ -339,6 +340,10 @@ class WalkerContext:
     def set_overlap_groups(self, groups: int):
         """Walker ranges whose launch chains overlap on separate streams (default 1)."""
         self._ck(lib().mrisim_set_overlap_groups(self._h, groups))
+
+    def set_task_steps(self, steps: int):
+        """Steps per task inside a launch of the fused kernel (<0: default, 0: off), see include/mrisim.h."""
+        self._ck(lib().mrisim_set_task_steps(self._h, steps))
 
     def set_scene(self, box: BacteriaBox):
         self._ck(lib().mrisim_set_scene(self._h, box._handle()))
