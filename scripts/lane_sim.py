@@ -97,6 +97,32 @@ def main():
     print(f"in_cell share {inc1.mean():.3f}")
     np.save("/tmp/lane_sim_cnt.npy", cnt)
 
+    # risk-aware order: key = the largest resident count a walker STARTING in this leaf reached within a launch
+    # (estimated from launch 1), ties by own count, then leaf index
+    li0 = leaf_index[leaf0]                                   # [step][walker] leaf index, launch 1
+    c0 = leaf_cnt[li0]
+    reach = c0.max(axis=0)                                     # per walker: max count over launch 1
+    risk = np.zeros(len(leaf_cnt), np.int64)
+    np.maximum.at(risk, li0[0], reach)
+    risk = np.maximum(risk, leaf_cnt)
+    start_leaf = leaf_index[leaf0[-1]]
+    for name, key in (("risk, own count, leaf", (risk[start_leaf] * 256 + leaf_cnt[start_leaf]) * (1 << 20) + (len(leaf_cnt) - 1 - start_leaf)),
+                      ("risk, leaf", risk[start_leaf] * (1 << 20) + (len(leaf_cnt) - 1 - start_leaf))):
+        perm2 = np.argsort(-key, kind="stable")
+        c2 = cnt_of_node[leaf1][:, perm2].astype(np.int32)[:, :nw * 32].reshape(steps, nw, 32)
+        g2 = (c2 // 4).max(axis=2) * 4; r2 = c2 % 4
+        cost2 = g2 + 2 * (r2 >= 2).any(axis=2) + 1 * ((r2 & 1) == 1).any(axis=2)
+        print(f"order by ({name}): shipped structure {cost2.mean():.3f} per warp-step -> lanes {32 * total / (32 * cost2.sum()):.2f}")
+        wc = cost2.sum(axis=0)                                 # per warp cost over the launch
+        for lo in (0, nw // 2, nw * 3 // 4, nw * 7 // 8, nw - 1024):
+            seg = wc[lo:lo + 1024]
+            print(f"   warps {lo:6d}+1024: cost mean {seg.mean():7.0f} p50 {np.median(seg):7.0f} p99 {np.percentile(seg, 99):7.0f} max {seg.max():7d}")
+    wc = cost_shipped.sum(axis=0)
+    print("shipped order:")
+    for lo in (0, nw // 2, nw * 3 // 4, nw * 7 // 8, nw - 1024):
+        seg = wc[lo:lo + 1024]
+        print(f"   warps {lo:6d}+1024: cost mean {seg.mean():7.0f} p50 {np.median(seg):7.0f} p99 {np.percentile(seg, 99):7.0f} max {seg.max():7d}")
+
 
 if __name__ == "__main__":
     main()

@@ -129,6 +129,32 @@ def test_pipelined_path_mid_sizes_equal_fused(n):
     assert int(out[0][0]["in_cell"].sum()) > 0
 
 
+@pytest.mark.parametrize("variant", ["split", 0, 1, 2, 3, 4, 5, 6])
+def test_pipelined_path_variants_equal_fused(variant, monkeypatch):
+    """Every variant of the pipelined path's walk stage -- the split kernels (positions and kicks through HBM) and
+    walker_team_kernel with 1..4 walkers per warp, roomy and tight register targets -- leaves the walkers, RNG
+    states and block sums of the fused kernel, bit for bit: low-permeability membranes with walkers inside cells
+    (crossings end speculative trips), a ragged walker count, two chained sprints, intracellular kicks."""
+    if variant == "split":
+        monkeypatch.setenv("MRISIM_PIPE_SPLIT", "1")
+    else:
+        monkeypatch.setenv("MRISIM_TEAM_VARIANT", str(variant))
+    p = api.low_permeability(api.ParameterStruct(avoid_intracellular_throw=0))
+    box, _ = make(p, 12345)
+    box.rethrow_waters(5003, 77, True, p)
+    w0 = box.getWaters().copy()
+    out = []
+    for mode in (api.PATH_PIPELINE, api.PATH_FUSED):
+        ctx = gpu_ctx(p, box, w0)
+        ctx.set_path_mode(mode)
+        sig = np.concatenate([ctx.run_sprint(3000), ctx.run_sprint(2000)])
+        out.append((ctx.get_waters(), ctx.get_rng(), sig, ctx.pipeline_sprints))
+    assert out[0][3] == 2 and out[1][3] == 0
+    assert out[0][0].tobytes() == out[1][0].tobytes() and out[0][1].tobytes() == out[1][1].tobytes()
+    assert np.max(np.abs(out[0][2] - out[1][2])) <= 1e-9 * len(w0)
+    assert int(out[0][0]["in_cell"].sum()) > 0
+
+
 def test_path_mode_auto_and_fallbacks():
     """AUTO takes the pipelined path for few walkers and the fused one for many, for traces, and for
     sprints that do not start on an even step; mixing the paths sprint by sprint changes no walker."""
