@@ -213,13 +213,6 @@ int  mrisim_set_resort_steps(mrisim_ctx* ctx, int32_t steps);
  * streams, so that the tail of one range's kernel overlaps the body of another's (default 1 = a
  * single chain; 2 and 4 measured no faster on B200).  Per-walker results do not depend on it. */
 int  mrisim_set_overlap_groups(mrisim_ctx* ctx, int32_t groups);
-/* Tasks inside a launch (no reference analogue).  A launch of the fused kernel is cut into tasks of `steps`
- * timesteps per tile of 128 walkers; CTAs draw tasks from a counter in dispatch order (every tile's first task,
- * then every tile's second, ...) and hand the tile's state on through global memory, so that the end of a
- * launch is a tail of short tasks instead of whole-launch CTAs.  Per-walker results and the signal's bits do
- * not depend on it.  steps < 0: default (on for walker counts that fill the GPU several times over);
- * steps == 0: off; steps > 0: as given, whatever the walker count. */
-int  mrisim_set_task_steps(mrisim_ctx* ctx, int32_t steps);
 
 /* `p_array<Triple> dev_lattice(p.num_cells, simBox.getCells(), d.lattice)` (cuda_sim.cu:935,960) */
 int  mrisim_set_cells(mrisim_ctx* ctx, const double* xyz, int32_t num_cells);
@@ -412,6 +405,11 @@ int64_t mrisim_selftest_sqrt_div(int device, double lo, double hi, uint64_t n);
  * of the lookup-lattice coordinate int(x/cubeLength) (cuda_sim.cu:455-457): 15n coordinates in
  * [0, bound), random and on both sides of every boundary, against the IEEE-divide expressions. */
 int64_t mrisim_selftest_index(int device, double bound, int32_t hashDim, uint64_t n);
+
+/* The walker order between launches (no reference analogue) is a stable radix sort written for this library
+ * (csrc/mrisim.cu, sort_*_kernel).  Self-test: n pairs with `bits`-bit keys (runs of equal keys included)
+ * against std::stable_sort on the host; returns the number of positions that differ, -1 on a CUDA error. */
+int64_t mrisim_selftest_sort(int device, uint64_t n, int32_t bits, uint64_t seed);
 
 int mrisim_version(void);
 

@@ -67,7 +67,6 @@ def lib():
         "mrisim_pipeline_sprints": (C.c_uint64, [vp]),
         "mrisim_set_resort_steps": (C.c_int, [vp, i32]),
         "mrisim_set_overlap_groups": (C.c_int, [vp, i32]),
-        "mrisim_set_task_steps": (C.c_int, [vp, i32]),
         "mrisim_set_cells": (C.c_int, [vp, vp, i32]),
         "mrisim_set_lookup": (C.c_int, [vp, vp, i32, i32]),
         "mrisim_set_octree": (C.c_int, [vp, i32, i32, vp, i32, vp, u64, vp, u64]),
@@ -90,6 +89,7 @@ def lib():
         "mrisim_selftest_div": (i64, [C.c_int, dbl, u64]),
         "mrisim_selftest_sqrt_div": (i64, [C.c_int, dbl, dbl, u64]),
         "mrisim_selftest_index": (i64, [C.c_int, dbl, i32, u64]),
+        "mrisim_selftest_sort": (i64, [C.c_int, u64, i32, u64]),
         "mrisim_simulate_waters": (C.c_int, [C.c_char_p, PP, u64, u64, C.c_int, i64]),
         "mrisim_simulate_waters_multi": (C.c_int, [C.c_char_p, PP, u64, u64, C.POINTER(C.c_int), C.c_int, i64, i64, C.c_char_p, C.c_char_p]),
         "mrisim_check": (C.c_int, [vp]),
@@ -145,12 +145,12 @@ ABI_SYMBOLS = [
     "mrisim_scene_build", "mrisim_scene_build_gpu", "mrisim_octree_build_set_margin_scale", "mrisim_scene_load", "mrisim_scene_save", "mrisim_scene_free",
     "mrisim_scene_last_error", "mrisim_scene_cells", "mrisim_scene_mnps", "mrisim_scene_lookup",
     "mrisim_scene_waters", "mrisim_scene_octree", "mrisim_scene_rethrow_waters", "mrisim_scene_rethrow_waters_gpu",
-    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups", "mrisim_set_task_steps",
+    "mrisim_create", "mrisim_destroy", "mrisim_last_error", "mrisim_set_field_mode", "mrisim_set_path_mode", "mrisim_pipeline_sprints", "mrisim_set_resort_steps", "mrisim_set_overlap_groups",
     "mrisim_set_cells", "mrisim_set_lookup", "mrisim_set_octree", "mrisim_set_scene",
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_trace_sprint_kicks", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
-    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index",
+    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index", "mrisim_selftest_sort",
     "mrisim_simulate_waters_multi", "mrisim_check", "mrisim_submit_sprint", "mrisim_wait_sprint", "mrisim_stream_wait_sprint", "mrisim_pending_sprints",
     "mrisim_nccl_unique_id", "mrisim_comm_init_rank", "mrisim_comm_attach", "mrisim_comm_size", "mrisim_nccl_origin",
     "mrisim_get_order", "mrisim_set_order", "mrisim_walker_count", "mrisim_first_walker_id", "mrisim_walker_seed",
@@ -340,10 +340,6 @@ class WalkerContext:
     def set_overlap_groups(self, groups: int):
         """Walker ranges whose launch chains overlap on separate streams (default 1)."""
         self._ck(lib().mrisim_set_overlap_groups(self._h, groups))
-
-    def set_task_steps(self, steps: int):
-        """Steps per task inside a launch of the fused kernel (<0: default, 0: off), see include/mrisim.h."""
-        self._ck(lib().mrisim_set_task_steps(self._h, steps))
 
     def set_scene(self, box: BacteriaBox):
         self._ck(lib().mrisim_set_scene(self._h, box._handle()))

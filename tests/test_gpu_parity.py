@@ -205,33 +205,6 @@ def test_launch_granularity_and_overlap_groups_do_not_change_walkers(resort, gro
     assert np.max(np.abs(sig - rsig)) <= 1e-9 * len(w0)
 
 
-@pytest.mark.parametrize("resort,tasks,groups", [(125, 25, 1), (300, 64, 1), (250, 50, 2), (96, 7, 1)])
-def test_tasks_inside_a_launch_do_not_change_anything(resort, tasks, groups):
-    """A launch cut into ticketed tasks (tile state handed from CTA to CTA through global memory, here with
-    fewer tiles than resident CTAs, so that tasks do wait for their predecessors): walkers, RNG states AND the
-    signal's bits are those of whole-launch CTAs; a subsample is the oracle's."""
-    p = api.low_permeability(api.ParameterStruct(num_cells=60, bound=12, water_start_bound=8, hashDim=10, border=3,
-                                                  avoid_intracellular_throw=0, num_water=64))
-    box, orc = make(p, 17)
-    box.rethrow_waters(70001, 33)
-    w0 = box.getWaters().copy()
-    ctx = gpu_ctx(p, box, w0)
-    ctx.set_path_mode(api.PATH_FUSED); ctx.set_resort_steps(resort); ctx.set_overlap_groups(groups); ctx.set_task_steps(tasks)
-    sig = np.concatenate([ctx.run_sprint(2000), ctx.run_sprint(1000)])
-    ref = gpu_ctx(p, box, w0)
-    ref.set_path_mode(api.PATH_FUSED); ref.set_resort_steps(resort); ref.set_overlap_groups(groups); ref.set_task_steps(0)
-    rsig = np.concatenate([ref.run_sprint(2000), ref.run_sprint(1000)])
-    assert ref.get_waters().tobytes() == ctx.get_waters().tobytes()
-    assert ref.get_rng().tobytes() == ctx.get_rng().tobytes()
-    assert sig.tobytes() == rsig.tobytes()
-    sel = np.arange(0, len(w0), 53)
-    sub = w0[sel].copy()
-    rng = np.concatenate([orc.seed(1, SEED, int(i)) for i in sel])
-    orc.run_sprint(sub, rng, 0, 2000); orc.run_sprint(sub, rng, 2000, 1000)
-    assert_state_equal(ctx.get_waters()[sel], sub)
-    assert ctx.get_rng()[sel].tobytes() == rng.tobytes()
-
-
 def test_traced_sprint_with_short_launches():
     """Per-step trace (positions, flags, leaf indices) with 130-step launches and re-ordering."""
     p, seed, _ = CASES["tiny_noavoid_lowperm"]
@@ -460,6 +433,13 @@ def test_device_selftests_of_exact_arithmetic():
     # integer fast paths of the Morton word and the lookup-lattice coordinate
     for bound, h in ((30.0, 20), (30.0, 40), (10.0, 8), (7.3, 1290), (100.0, 3)):
         assert L.mrisim_selftest_index(0, bound, h, 20_000_000) == 0
+
+
+@pytest.mark.parametrize("n,bits", [(1, 8), (31, 3), (2048, 8), (2049, 17), (100_003, 17), (1 << 20, 17), (3_000_001, 19), (1 << 20, 32)])
+def test_walker_order_sort_is_a_stable_sort(n, bits):
+    """The library's own radix sort (it replaced CUB's so that it can share an SM with walker CTAs) against
+    std::stable_sort: every (key, value) pair in place, ragged sizes, tiles larger than 2048, keys of 3..32 bits."""
+    assert api.lib().mrisim_selftest_sort(0, n, bits, 1234 + n) == 0
 
 
 def test_error_paths():
