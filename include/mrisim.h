@@ -209,9 +209,10 @@ uint64_t mrisim_pipeline_sprints(const mrisim_ctx* ctx);   /* sprints that took 
  * travel with the walker index); only the association order of the signal sum changes.
  * steps < 0: default (125); steps == 0: one launch per sprint, walkers in array order. */
 int  mrisim_set_resort_steps(mrisim_ctx* ctx, int32_t steps);
-/* The walker array is cut into `groups` contiguous ranges whose launch chains run on separate
- * streams, so that the tail of one range's kernel overlaps the body of another's (default 1 = a
- * single chain; 2 and 4 measured no faster on B200).  Per-walker results do not depend on it. */
+/* The walker array is cut into `groups` contiguous ranges whose launch chains (sort, kernel, sort, ...)
+ * run on separate streams, so that the tail of one range's kernel and its sort overlap the body of
+ * another's.  Default 3 (B200, 1 Mi walkers: +11 % over one chain, 2..6 alike); a range never gets fewer
+ * than two CTAs per SM, so few walkers run as one chain.  Per-walker results do not depend on it. */
 int  mrisim_set_overlap_groups(mrisim_ctx* ctx, int32_t groups);
 
 /* `p_array<Triple> dev_lattice(p.num_cells, simBox.getCells(), d.lattice)` (cuda_sim.cu:935,960) */
