@@ -131,13 +131,12 @@ def test_pipelined_path_mid_sizes_equal_fused(n):
 
 @pytest.mark.parametrize("variant", ["split", 0, 1, 2, 3, 4, 5, 6])
 def test_pipelined_path_variants_equal_fused(variant, monkeypatch):
-    """Every variant of the pipelined path's walk stage -- the split kernels (positions and kicks through HBM) and
-    walker_team_kernel with 1..4 walkers per warp, roomy and tight register targets -- leaves the walkers, RNG
+    """Every variant of the pipelined path's walk stage -- the split kernels (the default: positions and kicks through
+    HBM) and the experimental walker_team_kernel with 1..4 walkers per warp, roomy and tight register targets -- leaves the walkers, RNG
     states and block sums of the fused kernel, bit for bit: low-permeability membranes with walkers inside cells
     (crossings end speculative trips), a ragged walker count, two chained sprints, intracellular kicks."""
-    if variant == "split":
-        monkeypatch.setenv("MRISIM_PIPE_SPLIT", "1")
-    else:
+    if variant != "split":
+        monkeypatch.setenv("MRISIM_PIPE_TEAM", "1")
         monkeypatch.setenv("MRISIM_TEAM_VARIANT", str(variant))
     p = api.low_permeability(api.ParameterStruct(avoid_intracellular_throw=0))
     box, _ = make(p, 12345)
