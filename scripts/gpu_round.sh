@@ -21,4 +21,6 @@ GROUPS=1 ncu --set full --clock-control none --import-source on -k regex:walker_
     python scripts/profile_case.py 1048576 1000 1 > $out/ncu_full.log 2>&1
 cat $out/plain_profile_case.log
 fi
+MRISIM_TIMELINE=$PWD/$out/timeline8_final.bin timeout 300 python scripts/profile_case.py 1048576 1000 1 2>&1 | grep short | tail -1
+for wl in cfg4b_dense8000cells_1Mi_waters_per_gpu default_scene_1Mi_waters_per_gpu cfg3_lowperm_100k_waters; do python bench.py --workload $wl --steps 3 --warmup 3 --no-cpu-baseline --no-small-configs > $out/bench_${wl%%_*}.json 2>> $out/bench.err; cut -c1-260 $out/bench_${wl%%_*}.json; echo; done
 tail -3 $out/pytest_gpu.log
