@@ -17,7 +17,9 @@ mode = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 wl = os.environ.get("WORKLOAD", bench.DEFAULT_WORKLOAD)
 box, p, _ = bench.get_scene(api, wl, 0, 1, lambda: None, device=0)
 waters = bench.throw_waters(box, p, walkers, 0, device=0)
-ctx = api.WalkerContext(p, 0); ctx.set_field_mode(mode); ctx.set_resort_steps(int(os.environ.get('RESORT', '-1'))); ctx.set_overlap_groups(int(os.environ.get('GROUPS', '1'))); ctx.set_scene(box); ctx.set_waters(waters, bench.WALKER_SEED)
+ctx = api.WalkerContext(p, 0); ctx.set_field_mode(mode); ctx.set_resort_steps(int(os.environ.get('RESORT', '-1')))
+if 'GROUPS' in os.environ: ctx.set_overlap_groups(int(os.environ['GROUPS']))          # default: the library's
+ctx.set_scene(box); ctx.set_waters(waters, bench.WALKER_SEED)
 for _ in range(pre):
     ctx.run_sprint(p.sprintSteps)
     print(f"pre-sprint kernel {ctx.last_sprint_kernel_ms():.1f} ms -> {walkers*p.sprintSteps/ctx.last_sprint_kernel_ms()*1e3:.3e} steps/s")
