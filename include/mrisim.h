@@ -188,7 +188,7 @@ enum {
  *            draws per (walker, draw-chunk) from GF(2) jump-ahead states, the position recursion
  *            with one WARP per walker (32 speculative steps per trip, membrane tests side by side),
  *            the field per (walker, step), ordered block sums.  Needs even pfreq and whole intervals.
- *   AUTO     PIPELINE up to 49 152 walkers, FUSED above (default). */
+ *   AUTO     PIPELINE up to 65 536 walkers, FUSED above (default). */
 enum {
     MRISIM_PATH_AUTO = 0,
     MRISIM_PATH_FUSED = 1,
