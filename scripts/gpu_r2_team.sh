@@ -10,12 +10,12 @@ t() { # label, env...
 }
 for wl in cfg1_default_4032_waters:4032 cfg2_8000_waters_intracellular_kick:8000; do
   export WORKLOAD=${wl%%:*}; N=${wl##*:}
-  t MRISIM_PIPE_SPLIT=1
-  for v in 0 1 2 3 4 5 6; do t MRISIM_TEAM_VARIANT=$v; done
-  t MRISIM_TEAM_VARIANT=-1
+  t MRISIM_PIPE_TEAM=0
+  for v in 0 1 2 3 4 5 6; do t MRISIM_PIPE_TEAM=1 MRISIM_TEAM_VARIANT=$v; done
+  t MRISIM_PIPE_TEAM=1 MRISIM_TEAM_VARIANT=-1
 done
 unset WORKLOAD
 for g in 1 2; do
-  MRISIM_TIMELINE=$PWD/$out/timeline8_groups$g.bin GROUPS=$g TASKS=0 timeout 300 python scripts/profile_case.py 1048576 1000 1 2>&1 | grep -E "short" | tail -1
+  MRISIM_TIMELINE=$PWD/$out/timeline8_groups$g.bin WGROUPS=$g TASKS=0 timeout 300 python scripts/profile_case.py 1048576 1000 1 2>&1 | grep -E "short" | tail -1
 done
 ls -la $out

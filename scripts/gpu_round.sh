@@ -16,8 +16,8 @@ python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $out/plain_bench.log 2>
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $out/launches.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $out/ncu_launches.log 2>&1
 # the instruction mix is a property of the walkers, not of how their launches overlap: captured with ONE group (all walkers in one launch)
-GROUPS=1 python scripts/profile_case.py 1048576 1000 1 > $out/plain_profile_case.log 2>&1 &&
-GROUPS=1 ncu --set full --clock-control none --import-source on -k regex:walker_sprint -s 165 -c 1 -o $out/prof \
+WGROUPS=1 python scripts/profile_case.py 1048576 1000 1 > $out/plain_profile_case.log 2>&1 &&
+WGROUPS=1 ncu --set full --clock-control none --import-source on -k regex:walker_sprint -s 165 -c 1 -o $out/prof \
     python scripts/profile_case.py 1048576 1000 1 > $out/ncu_full.log 2>&1
 cat $out/plain_profile_case.log
 fi

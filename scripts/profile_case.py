@@ -18,7 +18,7 @@ wl = os.environ.get("WORKLOAD", bench.DEFAULT_WORKLOAD)
 box, p, _ = bench.get_scene(api, wl, 0, 1, lambda: None, device=0)
 waters = bench.throw_waters(box, p, walkers, 0, device=0)
 ctx = api.WalkerContext(p, 0); ctx.set_field_mode(mode); ctx.set_resort_steps(int(os.environ.get('RESORT', '-1')))
-if 'GROUPS' in os.environ: ctx.set_overlap_groups(int(os.environ['GROUPS']))          # default: the library's
+if 'WGROUPS' in os.environ: ctx.set_overlap_groups(int(os.environ['WGROUPS']))    # default: the library's (not GROUPS: bash keeps that name to itself and ignores assignments)
 ctx.set_scene(box); ctx.set_waters(waters, bench.WALKER_SEED)
 for _ in range(pre):
     ctx.run_sprint(p.sprintSteps)
