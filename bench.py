@@ -512,10 +512,58 @@ def main():
     if world == 1 and args.workload == DEFAULT_WORKLOAD and not args.no_small_configs:
         ctx.close()
         line["small_configs"] = small_configs(api, torch, local, args)
+        if not args.no_cpu_baseline:
+            line["reference_gpu"] = reference_gpu_block(api, torch, local)
     emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def reference_gpu_block(api, torch, local):
+    """Informational (part of the reported-baseline leg, like cpu_baseline): the reference's OWN GPU code -- cuda_sim.cu +
+    gpu_random.cu (cuRAND) + cuBLAS dgemv + thrust::reduce, compiled for sm_100 where it lies by `make -C oracle refgpu`
+    (oracle/_ref/ref_gpu_short: the SHIPPED parameters.h -- 4032 waters, sprints of 20 000 steps -- cut to the first 2 of its
+    40 ms) -- run on this GPU, next to this library on the same configuration.  Its walker randomness is cuRAND seeded from the clock, so the two runs agree
+    statistically only (tests/test_ref_gpu_crosscheck.py); the bit-level pin is tests/test_ref_gpu_bitpin.py."""
+    import re
+    import subprocess
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_short")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/ref_gpu_short not built (make -C oracle refgpu needs the reference tree)"}
+    n, sprint, total_ms = 4032, 20000, 2
+    steps_total = total_ms * 1_000_000                        # tau = 1e-6 ms per step (parameters.h)
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            out = subprocess.run([exe, os.path.join(tmp, "ref.csv")], capture_output=True, text=True, timeout=300, cwd=tmp)
+        m = re.search(r"Elapsed time: ([0-9.eE+]+) ms", out.stdout)
+        if out.returncode != 0 or not m:
+            return {"unavailable": "reference GPU binary failed: " + (out.stderr or out.stdout)[-200:]}
+        ref_ms = float(m.group(1))
+    except Exception as e:                                     # informational: never fail the bench line
+        return {"unavailable": f"reference GPU binary: {e}"}
+    p = api.ParameterStruct(num_water=n, sprintSteps=sprint, totaltime=total_ms)
+    assert p.t == steps_total
+    box = api.BacteriaBox(p, 12345).populateSimulation(device=local)
+    ctx = api.WalkerContext(p, local)
+    ctx.set_scene(box)
+    ctx.set_waters(box.getWaters().copy(), WALKER_SEED)
+    ctx.run_sprint(sprint)                                     # warm-up (buffers, jump tables)
+    ctx.set_waters(box.getWaters().copy(), WALKER_SEED)
+    torch.cuda.synchronize()
+    t = time.perf_counter()
+    for _ in range(steps_total // sprint):
+        ctx.run_sprint(sprint)
+    torch.cuda.synchronize()
+    our_ms = (time.perf_counter() - t) * 1e3
+    ctx.close()
+    return {"config": f"shipped parameters.h (BASELINE configs[0]) cut to {total_ms} of its 40 ms: {n} waters, {steps_total} steps in sprints of {sprint} (oracle/Makefile GCFG_short)",
+            "reference_gpu_code": {"value": n * steps_total / (ref_ms * 1e-3), "unit": "walker-steps/s", "ms": ref_ms,
+                                   "what": "the reference's cuda_sim.cu + cuRAND + cuBLAS + thrust recompiled for sm_100, its own 'Elapsed time' (sprint loop)"},
+            "this_library": {"value": n * steps_total / (our_ms * 1e-3), "unit": "walker-steps/s", "ms": our_ms,
+                             "what": f"mrisim_run_sprint x {steps_total // sprint}, wall clock incl. the signal samples read back after every sprint"},
+            "ratio": ref_ms / our_ms}
 
 
 def kernel_source_digest():
