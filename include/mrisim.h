@@ -412,6 +412,20 @@ int64_t mrisim_selftest_index(int device, double bound, int32_t hashDim, uint64_
  * against std::stable_sort on the host; returns the number of positions that differ, -1 on a CUDA error. */
 int64_t mrisim_selftest_sort(int device, uint64_t n, int32_t bits, uint64_t seed);
 
+/* The signal sample -- sum over n walkers of cos(phase), the reference's cosine + thrust::reduce step -- WITHOUT any
+ * allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  phase_dev: n phases in DEVICE memory of `device`; signal_out_dev: one double in device memory;
+ * both kernels are enqueued on `cuda_stream` (a cudaStream_t, NULL = the default stream) and the call returns
+ * without synchronising.  The per-CTA partials live in a static device array of 32 KB that every GPU loading the
+ * library holds until exit: n is limited to 16 777 216 walkers (larger n: nonzero return, mrisim_last_error(NULL)
+ * says so; split the walkers and add the parts).  The call makes no cudaMalloc / cudaFree and calls no allocating
+ * library routine; the first call per device resolves the array's address (cudaGetSymbolAddress) -- make it outside
+ * a stream capture.  All calls share the array: calls that overlap on the GPU (different streams) race on it;
+ * nothing in it needs clearing between calls.  Result: within 1e-6 * n of a context's signal sample (association
+ * order of the sum only); deterministic for a given n.  Returns 0 on success. */
+int mrisim_signal_sample_static(int device, const double* phase_dev, uint64_t n, double* signal_out_dev, void* cuda_stream);
+
 int mrisim_version(void);
 
 #ifdef __cplusplus

@@ -90,6 +90,7 @@ def lib():
         "mrisim_selftest_sqrt_div": (i64, [C.c_int, dbl, dbl, u64]),
         "mrisim_selftest_index": (i64, [C.c_int, dbl, i32, u64]),
         "mrisim_selftest_sort": (i64, [C.c_int, u64, i32, u64]),
+        "mrisim_signal_sample_static": (C.c_int, [C.c_int, vp, u64, vp, vp]),
         "mrisim_simulate_waters": (C.c_int, [C.c_char_p, PP, u64, u64, C.c_int, i64]),
         "mrisim_simulate_waters_multi": (C.c_int, [C.c_char_p, PP, u64, u64, C.POINTER(C.c_int), C.c_int, i64, i64, C.c_char_p, C.c_char_p]),
         "mrisim_check": (C.c_int, [vp]),
@@ -150,7 +151,7 @@ ABI_SYMBOLS = [
     "mrisim_set_waters", "mrisim_get_waters", "mrisim_get_rng", "mrisim_set_rng",
     "mrisim_get_time", "mrisim_set_time", "mrisim_run_sprint", "mrisim_run_sprint_async", "mrisim_ctx_stream",
     "mrisim_trace_sprint", "mrisim_trace_sprint_kicks", "mrisim_kernel_launches", "mrisim_last_sprint_kernel_ms",
-    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index", "mrisim_selftest_sort",
+    "mrisim_csv_row", "mrisim_simulate_waters", "mrisim_measure_fp64_tflops", "mrisim_selftest_div", "mrisim_selftest_sqrt_div", "mrisim_selftest_index", "mrisim_selftest_sort", "mrisim_signal_sample_static",
     "mrisim_simulate_waters_multi", "mrisim_check", "mrisim_submit_sprint", "mrisim_wait_sprint", "mrisim_stream_wait_sprint", "mrisim_pending_sprints",
     "mrisim_nccl_unique_id", "mrisim_comm_init_rank", "mrisim_comm_attach", "mrisim_comm_size", "mrisim_nccl_origin",
     "mrisim_get_order", "mrisim_set_order", "mrisim_walker_count", "mrisim_first_walker_id", "mrisim_walker_seed",
